@@ -154,6 +154,8 @@ int rtb_scene_add_mesh(rtb_ctx *ctx, const float *tri_points, const float *tri_u
  * (src/dispatch.cu:107), ReadOnlyDeviceArray<Object>/<Triangle> (src/main.cu:145,292) and the
  * host BVH constructor (src/objects.cu:452-464). */
 int rtb_scene_commit(rtb_ctx *ctx);
+/* rtb_scene_begin + one add per object of `desc` (same order) + rtb_scene_commit, in one call */
+int rtb_scene_set(rtb_ctx *ctx, const RtbSceneDesc *desc);
 /* view of the host-side description held by ctx (valid until the next rtb_scene_begin/destroy) */
 int rtb_scene_desc(rtb_ctx *ctx, RtbSceneDesc *out);
 

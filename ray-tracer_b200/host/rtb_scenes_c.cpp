@@ -1,0 +1,64 @@
+// rtb_scenes_c.cpp -- C entry points over the scene fixtures (scenes.hpp compiled against
+// rtb_compat.hpp) so that Python (tests, bench.py) can obtain an RtbSceneDesc / camera for a scene
+// id and hand it to librtb.so.  Host-only; built into librtb_scenes.so.
+#include "rtb_compat.hpp"
+#include "scenes.hpp"
+
+namespace {
+struct Handle {
+    rtb_compat::SceneDescStorage storage;
+    bool use_sky = false;
+};
+std::string g_err;
+}  // namespace
+
+extern "C" {
+
+const char *rtbs_last_error() { return g_err.c_str(); }
+
+void *rtbs_build(int scene_id, int p0, int p1, const char *models_dir) {
+    try {
+        rtb_compat::state().images.clear();
+        rtb_scenes::models_dir() = models_dir;
+        rtb_scenes::Scene s = rtb_scenes::build(scene_id, p0, p1);
+        Handle *h = new Handle();
+        rtb_compat::build_desc(s.objects.data(), (int)s.objects.size(), h->storage);
+        // the image store is process-wide: take private copies so the handle stays valid
+        static std::vector<std::vector<float>> keep;
+        for (RtbImage &img : h->storage.images) {
+            keep.emplace_back(img.rgb, img.rgb + (size_t)img.width * img.height * 3);
+            img.rgb = keep.back().data();
+        }
+        h->use_sky = s.use_sky;
+        return h;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+
+int rtbs_desc(void *handle, RtbSceneDesc *out) {
+    if (!handle) return 1;
+    *out = static_cast<Handle *>(handle)->storage.desc;
+    return 0;
+}
+
+int rtbs_use_sky(void *handle) { return handle && static_cast<Handle *>(handle)->use_sky ? 1 : 0; }
+
+void rtbs_free(void *handle) { delete static_cast<Handle *>(handle); }
+
+// Camera().get_cam_data() at the default pose for a run-time resolution (src/camera.cu:46-108)
+void rtbs_default_camera(int width, int height, RtbCamData *out) {
+    rtb_compat::set_resolution(width, height);
+    DeviceCamData d = Camera().get_cam_data();
+    *out = RtbCamData{rtb_compat::to_rtb(d.cam_pos), rtb_compat::to_rtb(d.tl_pixel_pos), rtb_compat::to_rtb(d.delta_u),
+                      rtb_compat::to_rtb(d.delta_v)};
+}
+
+// src/main.cu:13,318-330
+void rtbs_render_settings(int use_sky, int spp, int bounces, int antialias, RtbRenderData *out) {
+    RenderData r = rtb_scenes::render_settings(use_sky != 0, spp, bounces, antialias != 0);
+    *out = RtbRenderData{r.rays_per_pixel, r.reflection_limit, r.antialias ? 1 : 0, rtb_compat::to_rtb(r.sky_colour)};
+}
+
+}  // extern "C"
