@@ -66,6 +66,7 @@ float pto_normal(unsigned int *state) {
 typedef struct {
     V3 p0, side1, side2, normal; /* Triangle::precompute, objects.cu:175-186 */
     float uv[6];                 /* texture_points[3] */
+    V3 p1, p2;                   /* kept for the reference-BVH boxes below */
 } Tri;
 
 typedef struct {
@@ -73,6 +74,7 @@ typedef struct {
     V3 center; float radius;     /* SPHERE */
     int tri_first, tri_count;    /* into PtoScene.tris: TRIANGLE 1, QUAD/ONE_WAY 2, CUBOID 12, MESH n */
     V3 one_way_normal;
+    struct RefBvhTag *ref_bvh;   /* MESH: the reference's boxes (see ref_bvh_build) */
 } Obj;
 
 struct PtoScene {
@@ -89,6 +91,7 @@ static Tri make_tri(V3 a, V3 b, V3 c, const float *uv) {
     t.side2 = vsub(c, a);
     t.normal = vnorm(vcross(t.side1, t.side2));
     for (int i = 0; i < 6; i++) t.uv[i] = uv ? uv[i] : 0.f;
+    t.p1 = b; t.p2 = c;
     return t;
 }
 
@@ -111,6 +114,91 @@ static void make_cuboid(Tri *out, V3 tl_near, float width, float height, float d
     make_quad(out + 6, tr_near, br_near, br_far, tr_far);
     make_quad(out + 8, bl_near, br_near, br_far, bl_far);
     make_quad(out + 10, tl_near, tr_near, tr_far, tl_far);
+}
+
+/* ---- the reference's BVH boxes (culling is parity surface in degenerate cases) -----------------
+ * The reference reaches a mesh triangle only through the boxes on the path root -> leaf of its
+ * host-built BVH, each tested with BoundingBox::ray_hits (objects.cu:404-434): `tmin < tmax &&
+ * tmax > 0`, strict, with CUDA's NaN-dropping min/max.  For a generic ray a triangle hit implies
+ * that all those boxes are hit, so the tree is invisible.  Two degenerate cases are not:
+ *   (1) a box with zero extent on an axis (axis-aligned faces, e.g. the top/bottom of
+ *       models/cube.obj) gives t1 == t2, so tmin >= tmax and EVERY ray misses it;
+ *   (2) a zero direction component with the origin exactly on a box plane gives 0 * inf = NaN,
+ *       which min/max drop, and the box can be missed (row H/2 of an antialias-off render).
+ * To be exact the oracle rebuilds the reference's tree -- BVH::build :602-624, split_triangles
+ * :626-653 (first n/2+1 by distance of points[0] to the reference point go left), sort_triangles
+ * :655-706 (top-down merge sort taking the RIGHT element on ties), get_ref_point :708-719,
+ * BoundingBox::grow :369-393, fixed depth 10 (:786) -- and accepts a triangle hit only if every
+ * box on its path passes the reference's slab test.  (The traversal's distance culls, :501,:517,
+ * cannot reject a hit that is closer than the best so far and are not restated.)
+ */
+typedef struct { int idx; float dist; } RefPair;
+typedef struct { V3 lo, hi; int parent; } RefNode;
+typedef struct RefBvhTag { RefNode *nodes; int num_nodes, cap; int *leaf_of; /* per mesh triangle */ } RefBvh;
+
+static void ref_merge_sort(RefPair *a, int n, RefPair *tmp) {
+    if (n <= 1) return;
+    int mid = n / 2, nr = n - mid;
+    ref_merge_sort(a, mid, tmp);
+    ref_merge_sort(a + mid, nr, tmp);
+    int l = 0, r = 0;
+    for (int k = 0; k < n; k++) {
+        int add_left;
+        if (l >= mid) add_left = 0;
+        else if (r >= nr) add_left = 1;
+        else add_left = a[l].dist < a[mid + r].dist;
+        tmp[k] = add_left ? a[l++] : a[mid + r++];
+    }
+    memcpy(a, tmp, sizeof(RefPair) * n);
+}
+
+/* returns the node index, -1 for an empty subtree (the reference creates empty nodes whose boxes
+ * are (0,0,0)-(0,0,0): degenerate, never hit, and they hold no triangles) */
+static int ref_bvh_build(RefBvh *bvh, const Tri *tris, RefPair *items, int n, int depth, RefPair *tmp) {
+    if (n == 0) return -1;
+    V3 lo = tris[items[0].idx].p0, hi = lo;
+    for (int i = 0; i < n; i++) {
+        const Tri *t = &tris[items[i].idx];
+        V3 pts[3] = {t->p0, t->p1, t->p2};
+        for (int k = 0; k < 3; k++) {
+            lo.x = fminf(lo.x, pts[k].x); lo.y = fminf(lo.y, pts[k].y); lo.z = fminf(lo.z, pts[k].z);
+            hi.x = fmaxf(hi.x, pts[k].x); hi.y = fmaxf(hi.y, pts[k].y); hi.z = fmaxf(hi.z, pts[k].z);
+        }
+    }
+    if (bvh->num_nodes == bvh->cap) {
+        bvh->cap = bvh->cap ? bvh->cap * 2 : 256;
+        bvh->nodes = (RefNode *)realloc(bvh->nodes, sizeof(RefNode) * bvh->cap);
+    }
+    int me = bvh->num_nodes++;
+    bvh->nodes[me].lo = lo; bvh->nodes[me].hi = hi; bvh->nodes[me].parent = -1;
+    if (depth <= 0) {
+        for (int i = 0; i < n; i++) bvh->leaf_of[items[i].idx] = me;
+        return me;
+    }
+    float w = hi.x - lo.x, h = hi.y - lo.y, d = hi.z - lo.z; /* update_dimensions :395-402 */
+    V3 ref;
+    if (w >= h && w >= d) ref = v3(lo.x + w / 2, lo.y, lo.z + d / 2);
+    else if (h >= w && h >= d) ref = v3(lo.x, lo.y + h / 2, lo.z + d / 2);
+    else ref = v3(lo.x + w / 2, lo.y + h / 2, lo.z);
+    for (int i = 0; i < n; i++) items[i].dist = vmag(vsub(tris[items[i].idx].p0, ref));
+    ref_merge_sort(items, n, tmp);
+    int nleft = n / 2 + 1; /* i <= mid */
+    if (nleft > n) nleft = n;
+    int l = ref_bvh_build(bvh, tris, items, nleft, depth - 1, tmp);
+    int r = ref_bvh_build(bvh, tris, items + nleft, n - nleft, depth - 1, tmp);
+    if (l >= 0) bvh->nodes[l].parent = me;
+    if (r >= 0) bvh->nodes[r].parent = me;
+    return me;
+}
+
+static RefBvh *ref_bvh_create(const Tri *tris, int n) {
+    RefBvh *bvh = (RefBvh *)calloc(1, sizeof *bvh);
+    bvh->leaf_of = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    RefPair *items = (RefPair *)malloc(sizeof(RefPair) * (size_t)(n > 0 ? n : 1)), *tmp = (RefPair *)malloc(sizeof(RefPair) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) { items[i].idx = i; items[i].dist = 0; bvh->leaf_of[i] = -1; }
+    ref_bvh_build(bvh, tris, items, n, 10, tmp);
+    free(items); free(tmp);
+    return bvh;
 }
 
 PtoScene *pto_scene_create(const RtbSceneDesc *d) {
@@ -165,7 +253,9 @@ PtoScene *pto_scene_create(const RtbSceneDesc *d) {
                     const float *uv = d->mesh_tri_uv ? d->mesh_tri_uv + (size_t)(o->tri_first + t) * 6 : NULL;
                     s->tris[k + t] = make_tri(v3(p[0], p[1], p[2]), v3(p[3], p[4], p[5]), v3(p[6], p[7], p[8]), uv);
                 }
-                q->tri_count = o->tri_count; break;
+                q->tri_count = o->tri_count;
+                q->ref_bvh = ref_bvh_create(&s->tris[k], o->tri_count);
+                break;
             default: q->tri_count = 0;
         }
         k += q->tri_count;
@@ -177,6 +267,8 @@ PtoScene *pto_scene_create(const RtbSceneDesc *d) {
 void pto_scene_destroy(PtoScene *s) {
     if (!s) return;
     for (int i = 0; i < s->num_images; i++) free((void *)s->images[i].rgb);
+    for (int i = 0; i < s->num_objects; i++)
+        if (s->objects[i].ref_bvh) { free(s->objects[i].ref_bvh->nodes); free(s->objects[i].ref_bvh->leaf_of); free(s->objects[i].ref_bvh); }
     free(s->images); free(s->tris); free(s->materials); free(s->objects); free(s);
 }
 
@@ -290,6 +382,24 @@ static Hit sphere_hit(const Obj *o, const Ray *r, int need_uv) {
     return h;
 }
 
+/* BoundingBox::ray_hits, objects.cu:404-434 (fminf/fmaxf == CUDA's NaN-dropping min/max) */
+static int ref_box_hit(const RefNode *b, const Ray *r) {
+    float tmin = 0, tmax = (float)PTO_INF;
+    float t1 = (b->lo.x - r->origin.x) * r->dir_inv.x, t2 = (b->hi.x - r->origin.x) * r->dir_inv.x;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    t1 = (b->lo.y - r->origin.y) * r->dir_inv.y; t2 = (b->hi.y - r->origin.y) * r->dir_inv.y;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    t1 = (b->lo.z - r->origin.z) * r->dir_inv.z; t2 = (b->hi.z - r->origin.z) * r->dir_inv.z;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    return tmin < tmax && tmax > 0;
+}
+
+static int ref_path_hit(const struct RefBvhTag *bvh, int tri, const Ray *r) {
+    for (int n = bvh->leaf_of[tri]; n >= 0; n = bvh->nodes[n].parent)
+        if (!ref_box_hit(&bvh->nodes[n], r)) return 0;
+    return 1;
+}
+
 /* Object::hit dispatch, objects.cu:827-842 */
 static Hit object_hit(const PtoScene *s, const Obj *o, const Ray *r) {
     int need_uv = s->materials[o->material].need_uv;
@@ -316,7 +426,7 @@ static Hit object_hit(const PtoScene *s, const Obj *o, const Ray *r) {
             Hit best = miss;
             for (int k = 0; k < o->tri_count; k++) {
                 Hit th = tri_hit(t + k, r, need_uv);
-                if (th.hits && th.dist < best.dist) { best = th; best.sub = k; }
+                if (th.hits && th.dist < best.dist && ref_path_hit(o->ref_bvh, k, r)) { best = th; best.sub = k; }
             }
             return best;
         }
