@@ -1,0 +1,311 @@
+"""ray-tracer_b200 -- Python binding (ctypes) of the B200-native path tracer's C ABI.
+
+Thin plumbing over ``librtb.so`` (include/rtb.h) and ``librtb_scenes.so`` (the scene fixtures built
+through the C++ compat header that mirrors the reference's scene API).  Used by tests/, bench.py and
+__graft_entry__.py.  There is NO fallback: importing works without a GPU (so the CPU suite can check
+that the library loads and exports every symbol), but creating a :class:`Tracer` raises unless a
+CUDA device is usable, and a missing ``librtb.so`` raises at import.
+
+The directory name contains a hyphen (the repository layout asks for it); import it through the
+``raytracer_b200`` shim module at the repository root.
+"""
+import ctypes
+import os
+import re
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REPO_ROOT = os.path.dirname(_HERE)
+
+
+class RtbError(RuntimeError):
+    """Mirrors the std::runtime_error the reference's check_cuda_error throws (src/utils.cu:5-10)."""
+
+
+def _load(name):
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        raise RtbError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       f"(there is no CPU fallback for the render path)")
+    return ctypes.CDLL(path)
+
+
+lib = _load("librtb.so")
+scenes_lib = _load("librtb_scenes.so")
+
+
+class Vec3(ctypes.Structure):
+    _fields_ = [("x", ctypes.c_float), ("y", ctypes.c_float), ("z", ctypes.c_float)]
+
+
+class CamData(ctypes.Structure):  # RtbCamData == DeviceCamData (src/camera.cu:12-18)
+    _fields_ = [("cam_pos", Vec3), ("tl_pixel_pos", Vec3), ("delta_u", Vec3), ("delta_v", Vec3)]
+
+
+class RenderData(ctypes.Structure):  # RtbRenderData == RenderData (src/raytracer.cu:4-12)
+    _fields_ = [("rays_per_pixel", ctypes.c_int), ("reflection_limit", ctypes.c_int), ("antialias", ctypes.c_int),
+                ("sky_colour", Vec3)]
+
+
+class Texture(ctypes.Structure):
+    _fields_ = [("type", ctypes.c_int), ("colour", Vec3), ("light", Vec3), ("dark", Vec3), ("num_squares", ctypes.c_int),
+                ("img_width", ctypes.c_int), ("img_height", ctypes.c_int), ("image", ctypes.c_int)]
+
+
+class Material(ctypes.Structure):
+    _fields_ = [("type", ctypes.c_int), ("texture", Texture), ("smoothness", ctypes.c_float), ("need_uv", ctypes.c_int),
+                ("emitted_light", Vec3), ("refractive_index", ctypes.c_float)]
+
+
+class Object(ctypes.Structure):
+    _fields_ = [("type", ctypes.c_int), ("material", ctypes.c_int), ("p", Vec3 * 4), ("f", ctypes.c_float * 3),
+                ("uv", ctypes.c_float * 6), ("invert_normal", ctypes.c_int), ("tri_first", ctypes.c_int),
+                ("tri_count", ctypes.c_int)]
+
+
+class Image(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_int), ("height", ctypes.c_int), ("rgb", ctypes.POINTER(ctypes.c_float))]
+
+
+class SceneDesc(ctypes.Structure):
+    _fields_ = [("num_objects", ctypes.c_int), ("objects", ctypes.POINTER(Object)),
+                ("num_materials", ctypes.c_int), ("materials", ctypes.POINTER(Material)),
+                ("num_mesh_tris", ctypes.c_int), ("mesh_tri_points", ctypes.POINTER(ctypes.c_float)),
+                ("mesh_tri_uv", ctypes.POINTER(ctypes.c_float)),
+                ("num_images", ctypes.c_int), ("images", ctypes.POINTER(Image))]
+
+
+class Counters(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_ulonglong) for n in ("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+def declared_symbols(header=os.path.join(REPO_ROOT, "include", "rtb.h")):
+    """Every function name include/rtb.h declares (used by the symbol-export test)."""
+    text = open(header).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rtb_[a-z_0-9]+)\s*\(", text)))
+
+
+_vp, _i, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+_fp, _ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)
+lib.rtb_last_error.restype = ctypes.c_char_p
+lib.rtb_last_error.argtypes = [_vp]
+lib.rtb_create.argtypes = [ctypes.POINTER(_vp), _i]
+lib.rtb_destroy.argtypes = [_vp]
+lib.rtb_destroy.restype = None
+lib.rtb_set_camera.argtypes = [_vp, ctypes.POINTER(CamData), _i, _i]
+lib.rtb_set_render_data.argtypes = [_vp, ctypes.POINTER(RenderData)]
+lib.rtb_scene_set.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+lib.rtb_scene_begin.argtypes = [_vp]
+lib.rtb_scene_commit.argtypes = [_vp]
+lib.rtb_scene_desc.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+lib.rtb_scene_add_material.argtypes = [_vp, ctypes.POINTER(Material)]
+lib.rtb_scene_add_image.argtypes = [_vp, _vp, _i, _i]
+lib.rtb_scene_add_sphere.argtypes = [_vp, _vp, _f, _i]
+lib.rtb_scene_add_triangle.argtypes = [_vp, _vp, _vp, _i]
+lib.rtb_scene_add_quad.argtypes = [_vp, _vp, _i]
+lib.rtb_scene_add_one_way_quad.argtypes = [_vp, _vp, _i, _i]
+lib.rtb_scene_add_cuboid.argtypes = [_vp, _vp, _f, _f, _f, _i]
+lib.rtb_scene_add_mesh.argtypes = [_vp, _vp, _vp, _i, _i]
+lib.rtb_render.argtypes = [_vp, _vp, _ip, _i]
+lib.rtb_render_device.argtypes = [_vp, _i, _i, _i]
+lib.rtb_sync.argtypes = [_vp]
+lib.rtb_reset_accumulation.argtypes = [_vp]
+lib.rtb_set_accumulation.argtypes = [_vp, _vp, _i]
+lib.rtb_download.argtypes = [_vp, _vp, _ip]
+lib.rtb_device_image.argtypes = [_vp]
+lib.rtb_device_image.restype = _vp
+lib.rtb_stream.argtypes = [_vp]
+lib.rtb_stream.restype = _vp
+lib.rtb_last_device_ms.argtypes = [_vp, _fp]
+lib.rtb_set_shard.argtypes = [_vp, _i, _i, _i]
+lib.rtb_shard_rows.argtypes = [_vp, _ip, _ip]
+lib.rtb_shard_pack.argtypes = [_vp, _vp]
+lib.rtb_shard_unpack.argtypes = [_vp, _vp]
+lib.rtb_primary_ids.argtypes = [_vp, _vp, _vp, _vp]
+lib.rtb_counters.argtypes = [_vp, ctypes.POINTER(Counters)]
+lib.rtb_set_option.argtypes = [_vp, ctypes.c_char_p, _i]
+lib.rtb_get_info.argtypes = [_vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
+
+scenes_lib.rtbs_build.restype = _vp
+scenes_lib.rtbs_build.argtypes = [_i, _i, _i, ctypes.c_char_p]
+scenes_lib.rtbs_desc.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+scenes_lib.rtbs_use_sky.argtypes = [_vp]
+scenes_lib.rtbs_free.argtypes = [_vp]
+scenes_lib.rtbs_free.restype = None
+scenes_lib.rtbs_last_error.restype = ctypes.c_char_p
+scenes_lib.rtbs_default_camera.argtypes = [_i, _i, ctypes.POINTER(CamData)]
+scenes_lib.rtbs_render_settings.argtypes = [_i, _i, _i, _i, ctypes.POINTER(RenderData)]
+
+
+def models_dir():
+    """Directory holding cube.obj / low_poly_monkey.obj (reference DATA, never committed here)."""
+    cands = [os.environ.get("RTB_MODELS_DIR"), os.path.join(REPO_ROOT, "oracle", "_ref", "models"),
+             "/root/reference/models"]
+    for c in cands:
+        if c and os.path.exists(os.path.join(c, "low_poly_monkey.obj")):
+            return c
+    raise RtbError("OBJ fixtures not found (set RTB_MODELS_DIR or run oracle/Makefile where /root/reference exists)")
+
+
+class Scene:
+    """One of the scene fixtures of host/scenes.hpp, built through the compat mirror of the reference API.
+
+    ids: 0 Cornell+monkey+sphere (C1/C3/C5), 1 reflection, 2 textures, 3 glass, 4 seeded random spheres
+    (p0 = count, p1 = seed), 5 cube+spheres (C2), 6 monkey grid (C4; p0 x p1 instances).
+    """
+
+    def __init__(self, scene_id, p0=0, p1=0, models=None):
+        needs_models = scene_id in (0, 5, 6)
+        mdir = (models or models_dir()) if needs_models else (models or "models")
+        self.handle = scenes_lib.rtbs_build(scene_id, p0, p1, mdir.encode())
+        if not self.handle:
+            raise RtbError(scenes_lib.rtbs_last_error().decode())
+        self.desc = SceneDesc()
+        scenes_lib.rtbs_desc(self.handle, ctypes.byref(self.desc))
+        self.use_sky = bool(scenes_lib.rtbs_use_sky(self.handle))
+        self.scene_id = scene_id
+
+    def render_settings(self, spp, bounces, antialias=True):
+        rd = RenderData()
+        scenes_lib.rtbs_render_settings(int(self.use_sky), spp, bounces, int(antialias), ctypes.byref(rd))
+        return rd
+
+    def __del__(self):
+        if getattr(self, "handle", None):
+            scenes_lib.rtbs_free(self.handle)
+            self.handle = None
+
+
+def default_camera(width, height):
+    cam = CamData()
+    scenes_lib.rtbs_default_camera(width, height, ctypes.byref(cam))
+    return cam
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Tracer:
+    """One rendering context on one CUDA device (rtb_ctx)."""
+
+    def __init__(self, device=0):
+        self.ctx = ctypes.c_void_p()
+        if lib.rtb_create(ctypes.byref(self.ctx), device) != 0:
+            msg = lib.rtb_last_error(None).decode()
+            self.ctx = None
+            raise RtbError(msg)
+        self.width = self.height = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RtbError(lib.rtb_last_error(self.ctx).decode())
+
+    def close(self):
+        if self.ctx:
+            lib.rtb_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        self.close()
+
+    def set_camera(self, cam, width, height):
+        self._check(lib.rtb_set_camera(self.ctx, ctypes.byref(cam), width, height))
+        self.width, self.height = width, height
+
+    def set_render_data(self, rd):
+        self._check(lib.rtb_set_render_data(self.ctx, ctypes.byref(rd)))
+        self.rd = rd
+
+    def set_scene(self, scene):
+        desc = scene.desc if isinstance(scene, Scene) else scene
+        self._check(lib.rtb_scene_set(self.ctx, ctypes.byref(desc)))
+
+    def setup(self, scene, width, height, spp, bounces, antialias=True):
+        self.set_camera(default_camera(width, height), width, height)
+        self.set_render_data(scene.render_settings(spp, bounces, antialias))
+        self.set_scene(scene)
+        return self
+
+    def set_option(self, key, value):
+        self._check(lib.rtb_set_option(self.ctx, key.encode(), int(value)))
+
+    def info(self, key):
+        v = ctypes.c_double()
+        self._check(lib.rtb_get_info(self.ctx, key.encode(), ctypes.byref(v)))
+        return v.value
+
+    def render(self, image, frame_num, time_ms):
+        """== render(VariableRenderData*, int) (src/dispatch.cu:156): image (H*W*3 float32, host) in/out."""
+        assert image.dtype == np.float32 and image.size == self.width * self.height * 3 and image.flags.c_contiguous
+        f = ctypes.c_int(frame_num)
+        self._check(lib.rtb_render(self.ctx, _ptr(image), ctypes.byref(f), time_ms))
+        return f.value
+
+    def render_device(self, n_frames, time0_ms, time_step_ms=1):
+        self._check(lib.rtb_render_device(self.ctx, n_frames, time0_ms, time_step_ms))
+
+    def sync(self):
+        self._check(lib.rtb_sync(self.ctx))
+
+    def reset(self):
+        self._check(lib.rtb_reset_accumulation(self.ctx))
+
+    def set_accumulation(self, image, frame_num):
+        self._check(lib.rtb_set_accumulation(self.ctx, _ptr(np.ascontiguousarray(image, np.float32)), frame_num))
+
+    def download(self):
+        img = np.empty((self.height, self.width, 3), np.float32)
+        f = ctypes.c_int()
+        self._check(lib.rtb_download(self.ctx, _ptr(img), ctypes.byref(f)))
+        return img, f.value
+
+    def device_ms(self):
+        ms = ctypes.c_float()
+        self._check(lib.rtb_last_device_ms(self.ctx, ctypes.byref(ms)))
+        return ms.value
+
+    def device_image_ptr(self):
+        p = lib.rtb_device_image(self.ctx)
+        if not p:
+            raise RtbError(lib.rtb_last_error(self.ctx).decode())
+        return p
+
+    def stream(self):
+        return lib.rtb_stream(self.ctx)
+
+    def set_shard(self, rank, world, band_rows=8):
+        self._check(lib.rtb_set_shard(self.ctx, rank, world, band_rows))
+
+    def shard_rows(self):
+        a, b = ctypes.c_int(), ctypes.c_int()
+        self._check(lib.rtb_shard_rows(self.ctx, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def shard_pack(self, dense_dev_ptr):
+        self._check(lib.rtb_shard_pack(self.ctx, dense_dev_ptr))
+
+    def shard_unpack(self, gathered_dev_ptr):
+        self._check(lib.rtb_shard_unpack(self.ctx, gathered_dev_ptr))
+
+    def primary_ids(self):
+        n = self.width * self.height
+        obj, sub, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        self._check(lib.rtb_primary_ids(self.ctx, _ptr(obj), _ptr(sub), _ptr(t)))
+        shape = (self.height, self.width)
+        return obj.reshape(shape), sub.reshape(shape), t.reshape(shape)
+
+    def counters(self):
+        c = Counters()
+        self._check(lib.rtb_counters(self.ctx, ctypes.byref(c)))
+        return c.as_dict()
+
+
+def shard_rows_host(height, rank, world, band_rows):
+    """Rows owned by `rank` under the row-cyclic band sharding (host mirror of rtb_set_shard)."""
+    return [y for y in range(height) if (y // band_rows) % world == rank]

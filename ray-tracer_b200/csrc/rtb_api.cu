@@ -1,0 +1,780 @@
+// rtb_api.cu -- the extern "C" launch layer of librtb.so (include/rtb.h): context, scene
+// flattening (Object[] -> SoA primitive records + material table, creation order preserved),
+// GPU LBVH build, persistent device buffers, render entry points.  Replaces src/dispatch.cu of the
+// reference (per-frame cudaMalloc/cudaMallocManaged/cudaFree, element-wise managed-memory copy out,
+// three __constant__ symbols).  No CPU fallback: every entry point needs a working CUDA device.
+#include "../../include/rtb.h"
+#include "rtb_launch.h"
+#include "rtb_lbvh.h"
+#include "rtb_refbvh.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace rtb;
+
+namespace {
+std::string g_create_error;
+}
+
+struct rtb_ctx {
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+
+    int width = 0, height = 0;
+    bool have_cam = false, have_rd = false;
+    RtbCamData cam{};
+    RtbRenderData rd{};
+
+    // host-side scene description (owned copies)
+    std::vector<RtbObject> objects;
+    std::vector<RtbMaterial> materials;
+    std::vector<float> tri_points, tri_uv;
+    std::vector<std::vector<float>> image_data;
+    std::vector<RtbImage> images;
+    bool committed = false;
+
+    // device scene
+    DScene d{};
+    std::vector<void *> scene_allocs;
+    double build_ms = 0;
+    size_t scene_bytes = 0;
+    int culled_tris = 0;
+
+    // frame state
+    float *d_image = nullptr;
+    size_t image_floats = 0;
+    int frame_num = 0;
+    unsigned int *d_work = nullptr;
+    unsigned long long *d_counters = nullptr;
+    RtbCounters last_counters{};
+    bool timing_pending = false;
+
+    // options
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1;
+    int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
+    int shard_rank = 0, shard_world = 1, band_rows = 8;
+};
+
+namespace {
+
+int fail(rtb_ctx *ctx, const char *where, const char *msg) {
+    std::string s = std::string("Error from CUDA (") + where + "): " + msg;  // check_cuda_error shape, utils.cu:5-10
+    if (ctx) ctx->err = s; else g_create_error = s;
+    return 1;
+}
+
+#define RTB_CUDA(ctx, call, where)                                           \
+    do {                                                                     \
+        cudaError_t e_ = (call);                                             \
+        if (e_ != cudaSuccess) return fail(ctx, where, cudaGetErrorString(e_)); \
+    } while (0)
+
+struct Bind {  // make ctx's device current for the duration of a call
+    int prev = -1;
+    explicit Bind(rtb_ctx *c) {
+        cudaGetDevice(&prev);
+        if (prev != c->device) cudaSetDevice(c->device);
+    }
+};
+
+void free_scene(rtb_ctx *c) {
+    for (void *p : c->scene_allocs) cudaFree(p);
+    c->scene_allocs.clear();
+    c->d = DScene{};
+    c->committed = false;
+    c->scene_bytes = 0;
+}
+
+template <typename T> cudaError_t upload(rtb_ctx *c, const std::vector<T> &v, const T **out) {
+    *out = nullptr;
+    size_t bytes = sizeof(T) * (v.empty() ? 1 : v.size());
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    c->scene_allocs.push_back(p);
+    c->scene_bytes += bytes;
+    if (!v.empty()) e = cudaMemcpyAsync(p, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice, c->stream);
+    *out = (const T *)p;
+    return e;
+}
+
+// ---- host float helpers: the expressions of Triangle::precompute (objects.cu:175-186) ----------
+struct H3 {
+    float x, y, z;
+};
+inline H3 hsub(H3 a, H3 b) { return H3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline H3 hadd(H3 a, H3 b) { return H3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline H3 hcross(H3 a, H3 b) { return H3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline H3 hnorm(H3 a) {
+    float mag_sq = a.x * a.x + a.y * a.y + a.z * a.z;
+    float inv = 1 / sqrtf(mag_sq);
+    return H3{a.x * inv, a.y * inv, a.z * inv};
+}
+inline H3 h3(RtbVec3 v) { return H3{v.x, v.y, v.z}; }
+
+struct TriRec {
+    float4 a, b, c;
+    H3 normal;
+};
+TriRec make_tri(H3 p0, H3 p1, H3 p2) {
+    H3 s1 = hsub(p1, p0), s2 = hsub(p2, p0);
+    H3 n = hnorm(hcross(s1, s2));
+    TriRec t;
+    t.a = make_float4(p0.x, p0.y, p0.z, s1.x);
+    t.b = make_float4(s1.y, s1.z, s2.x, s2.y);
+    t.c = make_float4(s2.z, n.x, n.y, n.z);
+    t.normal = n;
+    return t;
+}
+
+struct Flat {
+    std::vector<float4> tris, quads, spheres, ref_nodes;
+    std::vector<int2> tri_ids, quad_ids;
+    std::vector<float2> tri_uv;
+    std::vector<int> tri_refleaf, sphere_ids, obj_material, leaf_refs;
+    std::vector<DMaterial> materials;
+    std::vector<float> image_rgb;
+    int culled = 0;
+
+    void add_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
+        int idx = (int)tri_ids.size();
+        tris.push_back(t.a); tris.push_back(t.b); tris.push_back(t.c);
+        tri_ids.push_back(make_int2(obj, sub));
+        for (int k = 0; k < 3; k++) tri_uv.push_back(uv ? make_float2(uv[2 * k], uv[2 * k + 1]) : make_float2(0, 0));
+        tri_refleaf.push_back(refleaf);
+        leaf_refs.push_back(~((idx << 2) | KIND_TRI));
+    }
+    // Quad::create_triangles (objects.cu:244-253): t1 = (p1,p2,p3), t2 = (p1,p4,p3)
+    void add_quad(H3 p1, H3 p2, H3 p3, H3 p4, int obj, int sub, bool one_way, bool invert) {
+        int idx = (int)quad_ids.size();
+        TriRec A = make_tri(p1, p2, p3), B = make_tri(p1, p4, p3);
+        quads.push_back(A.a); quads.push_back(A.b); quads.push_back(A.c);
+        quads.push_back(B.a); quads.push_back(B.b); quads.push_back(B.c);
+        float m = (float)(1 - 2 * (invert ? 1 : 0));  // OneWayQuad::get_normal_vec, objects.cu:285-289
+        float4 ow = make_float4(A.normal.x * m, A.normal.y * m, A.normal.z * m, 0.f);
+        int flag = one_way ? 1 : 0;
+        std::memcpy(&ow.w, &flag, sizeof(int));
+        quads.push_back(ow);
+        quad_ids.push_back(make_int2(obj, sub));
+        leaf_refs.push_back(~((idx << 2) | KIND_QUAD));
+    }
+};
+
+int flatten(rtb_ctx *c, Flat &f) {
+    // image store -> one float array
+    std::vector<int> img_offset;
+    for (const RtbImage &img : c->images) {
+        img_offset.push_back((int)f.image_rgb.size());
+        f.image_rgb.insert(f.image_rgb.end(), img.rgb, img.rgb + (size_t)img.width * img.height * 3);
+    }
+    for (const RtbMaterial &m : c->materials) {
+        DMaterial d;
+        std::memset(&d, 0, sizeof d);
+        d.type = m.type;
+        d.tex_type = m.texture.type;
+        d.smoothness = m.smoothness;
+        d.refractive_index = m.refractive_index;
+        d.need_uv = m.need_uv;
+        d.num_squares = m.texture.num_squares;
+        if (m.texture.type == RTB_TEX_CHECKERBOARD) {
+            d.a[0] = m.texture.light.x; d.a[1] = m.texture.light.y; d.a[2] = m.texture.light.z;
+            d.b[0] = m.texture.dark.x; d.b[1] = m.texture.dark.y; d.b[2] = m.texture.dark.z;
+        } else {
+            d.a[0] = m.texture.colour.x; d.a[1] = m.texture.colour.y; d.a[2] = m.texture.colour.z;
+        }
+        if (m.type == RTB_MAT_EMISSIVE) { d.b[0] = m.emitted_light.x; d.b[1] = m.emitted_light.y; d.b[2] = m.emitted_light.z; }
+        if (m.texture.type == RTB_TEX_IMAGE) {
+            if (m.texture.image < 0 || m.texture.image >= (int)c->images.size()) return fail(c, "flattening scene", "material refers to an unknown image");
+            d.img_w = c->images[m.texture.image].width;
+            d.img_h = c->images[m.texture.image].height;
+            d.img_offset = img_offset[m.texture.image];
+        }
+        f.materials.push_back(d);
+    }
+    for (int i = 0; i < (int)c->objects.size(); i++) {
+        const RtbObject &o = c->objects[i];
+        if (o.material < 0 || o.material >= (int)c->materials.size()) return fail(c, "flattening scene", "object refers to an unknown material");
+        f.obj_material.push_back(o.material);
+        switch (o.type) {
+            case RTB_OBJ_SPHERE: {
+                int idx = (int)f.sphere_ids.size();
+                f.spheres.push_back(make_float4(o.p[0].x, o.p[0].y, o.p[0].z, o.f[0]));
+                f.sphere_ids.push_back(i);
+                f.leaf_refs.push_back(~((idx << 2) | KIND_SPHERE));
+                break;
+            }
+            case RTB_OBJ_TRIANGLE: f.add_tri(make_tri(h3(o.p[0]), h3(o.p[1]), h3(o.p[2])), i, 0, o.uv, -1); break;
+            case RTB_OBJ_QUAD: f.add_quad(h3(o.p[0]), h3(o.p[1]), h3(o.p[2]), h3(o.p[3]), i, 0, false, false); break;
+            case RTB_OBJ_ONE_WAY_QUAD: f.add_quad(h3(o.p[0]), h3(o.p[1]), h3(o.p[2]), h3(o.p[3]), i, 0, true, o.invert_normal != 0); break;
+            case RTB_OBJ_CUBOID: {  // Cuboid::create_faces, objects.cu:327-349
+                H3 tl_near = h3(o.p[0]), w{o.f[0], 0, 0}, h{0, o.f[1], 0}, d{0, 0, o.f[2]};
+                H3 tr_near = hadd(tl_near, w), br_near = hsub(tr_near, h), bl_near = hsub(tl_near, h);
+                H3 tl_far = hadd(tl_near, d), tr_far = hadd(tl_far, w), br_far = hsub(tr_far, h), bl_far = hsub(tl_far, h);
+                f.add_quad(tl_near, tr_near, br_near, bl_near, i, 0, false, false);
+                f.add_quad(tl_far, tr_far, br_far, bl_far, i, 2, false, false);
+                f.add_quad(tl_near, bl_near, bl_far, tl_far, i, 4, false, false);
+                f.add_quad(tr_near, br_near, br_far, tr_far, i, 6, false, false);
+                f.add_quad(bl_near, br_near, br_far, bl_far, i, 8, false, false);
+                f.add_quad(tl_near, tr_near, tr_far, tl_far, i, 10, false, false);
+                break;
+            }
+            case RTB_OBJ_MESH: {
+                if (o.tri_first < 0 || o.tri_count < 0 || (size_t)(o.tri_first + o.tri_count) * 9 > c->tri_points.size())
+                    return fail(c, "flattening scene", "mesh triangle range out of bounds");
+                const float *pts = c->tri_points.data() + (size_t)o.tri_first * 9;
+                RefBvh rb;
+                int node_base = (int)(f.ref_nodes.size() / 2);
+                if (c->opt_ref_quirks) {
+                    ref_bvh_partition(pts, o.tri_count, rb);
+                    for (const RefBvhNode &n : rb.nodes) {
+                        int parent = n.parent < 0 ? -1 : node_base + n.parent;
+                        float4 lo = make_float4(n.lo[0], n.lo[1], n.lo[2], 0.f);
+                        std::memcpy(&lo.w, &parent, sizeof(int));
+                        f.ref_nodes.push_back(lo);
+                        f.ref_nodes.push_back(make_float4(n.hi[0], n.hi[1], n.hi[2], 0.f));
+                    }
+                }
+                for (int k = 0; k < o.tri_count; k++) {
+                    if (c->opt_ref_quirks && rb.degenerate[k]) { f.culled++; continue; }  // invisible in the reference
+                    const float *p = pts + (size_t)k * 9;
+                    const float *uv = c->tri_uv.empty() ? nullptr : c->tri_uv.data() + (size_t)(o.tri_first + k) * 6;
+                    f.add_tri(make_tri(H3{p[0], p[1], p[2]}, H3{p[3], p[4], p[5]}, H3{p[6], p[7], p[8]}), i, k, uv,
+                              c->opt_ref_quirks ? node_base + rb.leaf_of[k] : -1);
+                }
+                break;
+            }
+            default: return fail(c, "flattening scene", "unknown object type");
+        }
+    }
+    return 0;
+}
+
+}  // namespace
+
+// ---- shard helpers ---------------------------------------------------------------------------------
+namespace {
+
+int shard_local_rows(const rtb_ctx *c, int rank) {
+    if (c->shard_world <= 1) return c->height;
+    int rows = 0;
+    for (int y = 0; y < c->height; y++)
+        if ((y / c->band_rows) % c->shard_world == rank) rows++;
+    return rows;
+}
+
+__global__ void shard_pack_kernel(const float *image, float *dense, int width, int local_rows, int rank, int world, int band_rows, int height) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int row_floats = width * 3;
+    if (i >= local_rows * row_floats) return;
+    int lr = i / row_floats, col = i - lr * row_floats;
+    int band = lr / band_rows, within = lr - band * band_rows;
+    int y = (band * world + rank) * band_rows + within;
+    if (y < height) dense[i] = image[(size_t)y * row_floats + col];
+}
+
+__global__ void shard_unpack_kernel(float *image, const float *gathered, int width, int rows_padded, int world, int band_rows, int height) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int row_floats = width * 3;
+    size_t per_rank = (size_t)rows_padded * row_floats;
+    if (i >= per_rank * world) return;
+    int rank = (int)(i / per_rank);
+    size_t j = i - (size_t)rank * per_rank;
+    int lr = (int)(j / row_floats), col = (int)(j - (size_t)lr * row_floats);
+    int band = lr / band_rows, within = lr - band * band_rows;
+    int y = (band * world + rank) * band_rows + within;
+    if (y < height) image[(size_t)y * row_floats + col] = gathered[i];
+}
+
+int ensure_image(rtb_ctx *c) {
+    size_t need = (size_t)c->width * c->height * 3;
+    if (need == 0) return fail(c, "allocating image", "camera/resolution not set");
+    if (c->image_floats != need) {
+        if (c->d_image) cudaFree(c->d_image);
+        c->d_image = nullptr;
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_image, need * sizeof(float)), "allocating image");
+        RTB_CUDA(c, cudaMemsetAsync(c->d_image, 0, need * sizeof(float), c->stream), "clearing image");
+        c->image_floats = need;
+        c->frame_num = 0;
+    }
+    return 0;
+}
+
+int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
+    RenderParams p;
+    p.scene = c->d;
+    std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
+    p.rd.rays_per_pixel = c->rd.rays_per_pixel;
+    p.rd.reflection_limit = c->rd.reflection_limit;
+    p.rd.antialias = c->rd.antialias;
+    p.rd.sky[0] = c->rd.sky_colour.x; p.rd.sky[1] = c->rd.sky_colour.y; p.rd.sky[2] = c->rd.sky_colour.z;
+    p.width = c->width; p.height = c->height;
+    p.time_ms = time_ms; p.frame_num = frame_num;
+    p.prev = c->d_image; p.out = c->d_image;
+    p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
+    p.local_rows = shard_local_rows(c, c->shard_rank);
+    p.work_counter = c->d_work;
+    p.counters = c->opt_counters ? c->d_counters : nullptr;
+    RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
+    LaunchConfig cfg;
+    cfg.threads = c->opt_threads;
+    int per_sm = c->opt_blocks_per_sm;
+    if (per_sm <= 0) {
+        cudaError_t e = c->opt_strict ? strict::render_occupancy(cfg.threads, &per_sm) : fast::render_occupancy(cfg.threads, &per_sm);
+        if (e != cudaSuccess || per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
+    }
+    cfg.blocks = c->num_sms * per_sm;
+    cudaError_t e = c->opt_strict ? strict::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream)
+                                  : fast::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream);
+    if (e != cudaSuccess) return fail(c, "launching render kernel", cudaGetErrorString(e));
+    return 0;
+}
+
+int check_ready(rtb_ctx *c) {
+    if (!c) return 1;
+    if (!c->have_cam) return fail(c, "render", "camera not set (rtb_set_camera)");
+    if (!c->have_rd) return fail(c, "render", "render data not set (rtb_set_render_data)");
+    if (!c->committed) return fail(c, "render", "scene not committed (rtb_scene_commit)");
+    return ensure_image(c);
+}
+
+}  // namespace
+
+// ======================================= extern "C" ==================================================
+extern "C" {
+
+int rtb_abi_version(void) { return RTB_ABI_VERSION; }
+
+const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int rtb_create(rtb_ctx **out, int device) {
+    if (!out) return fail(nullptr, "rtb_create", "null output pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess) return fail(nullptr, "rtb_create", cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(nullptr, "rtb_create", "no such CUDA device");
+    RTB_CUDA(nullptr, cudaSetDevice(device), "selecting device");
+    rtb_ctx *c = new rtb_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&c->d_work, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&c->d_counters, 6 * sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+        fail(nullptr, "rtb_create", cudaGetErrorString(e));
+        rtb_destroy(c);
+        return 1;
+    }
+    c->num_sms = prop.multiProcessorCount;
+    *out = c;
+    return 0;
+}
+
+void rtb_destroy(rtb_ctx *c) {
+    if (!c) return;
+    Bind b(c);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    if (c->d_image) cudaFree(c->d_image);
+    if (c->d_work) cudaFree(c->d_work);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int rtb_set_camera(rtb_ctx *c, const RtbCamData *cam, int width, int height) {
+    if (!c || !cam) return 1;
+    if (width <= 0 || height <= 0 || (long long)width * height * 3 > 0x7fffffffLL) return fail(c, "rtb_set_camera", "bad resolution");
+    c->cam = *cam;
+    c->width = width; c->height = height;
+    c->have_cam = true;
+    return 0;
+}
+
+int rtb_set_render_data(rtb_ctx *c, const RtbRenderData *rd) {
+    if (!c || !rd) return 1;
+    c->rd = *rd;
+    c->have_rd = true;
+    return 0;
+}
+
+int rtb_scene_begin(rtb_ctx *c) {
+    if (!c) return 1;
+    Bind b(c);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    c->objects.clear(); c->materials.clear(); c->tri_points.clear(); c->tri_uv.clear();
+    c->image_data.clear(); c->images.clear();
+    return 0;
+}
+
+int rtb_scene_add_material(rtb_ctx *c, const RtbMaterial *m) {
+    if (!c || !m) return -1;
+    c->materials.push_back(*m);
+    return (int)c->materials.size() - 1;
+}
+
+int rtb_scene_add_image(rtb_ctx *c, const float *rgb, int width, int height) {
+    if (!c || !rgb || width <= 0 || height <= 0) return -1;
+    c->image_data.emplace_back(rgb, rgb + (size_t)width * height * 3);
+    c->images.push_back(RtbImage{width, height, nullptr});
+    for (size_t i = 0; i < c->images.size(); i++) c->images[i].rgb = c->image_data[i].data();
+    return (int)c->images.size() - 1;
+}
+
+static int add_object(rtb_ctx *c, const RtbObject &o) {
+    if (!c) return -1;
+    if (o.material < 0 || o.material >= (int)c->materials.size()) { fail(c, "adding object", "unknown material index"); return -1; }
+    c->objects.push_back(o);
+    return (int)c->objects.size() - 1;
+}
+
+int rtb_scene_add_sphere(rtb_ctx *c, const float center[3], float radius, int material) {
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_SPHERE; o.material = material;
+    o.p[0] = RtbVec3{center[0], center[1], center[2]}; o.f[0] = radius;
+    return add_object(c, o);
+}
+
+int rtb_scene_add_triangle(rtb_ctx *c, const float pts[9], const float uv[6], int material) {
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_TRIANGLE; o.material = material;
+    for (int k = 0; k < 3; k++) o.p[k] = RtbVec3{pts[3 * k], pts[3 * k + 1], pts[3 * k + 2]};
+    if (uv) std::memcpy(o.uv, uv, sizeof o.uv);
+    return add_object(c, o);
+}
+
+int rtb_scene_add_quad(rtb_ctx *c, const float pts[12], int material) {
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_QUAD; o.material = material;
+    for (int k = 0; k < 4; k++) o.p[k] = RtbVec3{pts[3 * k], pts[3 * k + 1], pts[3 * k + 2]};
+    return add_object(c, o);
+}
+
+int rtb_scene_add_one_way_quad(rtb_ctx *c, const float pts[12], int invert_normal, int material) {
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_ONE_WAY_QUAD; o.material = material; o.invert_normal = invert_normal;
+    for (int k = 0; k < 4; k++) o.p[k] = RtbVec3{pts[3 * k], pts[3 * k + 1], pts[3 * k + 2]};
+    return add_object(c, o);
+}
+
+int rtb_scene_add_cuboid(rtb_ctx *c, const float tl_near[3], float width, float height, float depth, int material) {
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_CUBOID; o.material = material;
+    o.p[0] = RtbVec3{tl_near[0], tl_near[1], tl_near[2]};
+    o.f[0] = width; o.f[1] = height; o.f[2] = depth;
+    return add_object(c, o);
+}
+
+int rtb_scene_add_mesh(rtb_ctx *c, const float *tri_points, const float *tri_uv, int num_tris, int material) {
+    if (!c || num_tris < 0 || (num_tris > 0 && !tri_points)) return -1;
+    RtbObject o; std::memset(&o, 0, sizeof o);
+    o.type = RTB_OBJ_MESH; o.material = material;
+    o.tri_first = (int)(c->tri_points.size() / 9); o.tri_count = num_tris;
+    int idx = add_object(c, o);
+    if (idx < 0) return idx;
+    c->tri_points.insert(c->tri_points.end(), tri_points, tri_points + (size_t)num_tris * 9);
+    if (tri_uv) c->tri_uv.insert(c->tri_uv.end(), tri_uv, tri_uv + (size_t)num_tris * 6);
+    else c->tri_uv.insert(c->tri_uv.end(), (size_t)num_tris * 6, 0.f);
+    return idx;
+}
+
+int rtb_scene_commit(rtb_ctx *c) {
+    if (!c) return 1;
+    Bind b(c);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    Flat f;
+    if (flatten(c, f) != 0) return 1;
+    DScene d{};
+    RTB_CUDA(c, upload(c, f.tris, &d.tris), "uploading triangles");
+    RTB_CUDA(c, upload(c, f.tri_ids, &d.tri_ids), "uploading triangle ids");
+    RTB_CUDA(c, upload(c, f.tri_uv, &d.tri_uv), "uploading triangle uvs");
+    RTB_CUDA(c, upload(c, f.tri_refleaf, &d.tri_refleaf), "uploading reference leaves");
+    RTB_CUDA(c, upload(c, f.quads, &d.quads), "uploading quads");
+    RTB_CUDA(c, upload(c, f.quad_ids, &d.quad_ids), "uploading quad ids");
+    RTB_CUDA(c, upload(c, f.spheres, &d.spheres), "uploading spheres");
+    RTB_CUDA(c, upload(c, f.sphere_ids, &d.sphere_ids), "uploading sphere ids");
+    RTB_CUDA(c, upload(c, f.obj_material, &d.obj_material), "uploading object materials");
+    RTB_CUDA(c, upload(c, f.materials, &d.materials), "uploading materials");
+    RTB_CUDA(c, upload(c, f.image_rgb, &d.image_rgb), "uploading texture rgb values");
+    RTB_CUDA(c, upload(c, f.ref_nodes, &d.ref_nodes), "uploading reference boxes");
+    RTB_CUDA(c, upload(c, f.leaf_refs, &d.all_refs), "uploading primitive list");
+    d.num_prims = (int)f.leaf_refs.size();
+    d.num_tris = (int)f.tri_ids.size();
+    d.num_quads = (int)f.quad_ids.size();
+    d.num_spheres = (int)f.sphere_ids.size();
+    d.num_objects = (int)c->objects.size();
+    c->culled_tris = f.culled;
+
+    LbvhInput in;
+    in.num_prims = d.num_prims;
+    in.leaf_refs = d.all_refs;
+    in.tris = d.tris; in.quads = d.quads; in.spheres = d.spheres;
+    float4 *nodes = nullptr;
+    int root = 0;
+    RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "timing LBVH build");
+    RTB_CUDA(c, lbvh_build(in, &nodes, &root, c->stream), "building LBVH");
+    RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "timing LBVH build");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "building LBVH");
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->build_ms = ms;
+    if (nodes) {
+        c->scene_allocs.push_back(nodes);
+        c->scene_bytes += sizeof(float4) * 4 * (size_t)(d.num_prims - 1);
+    }
+    d.nodes = nodes;
+    d.root_ref = root;
+    c->d = d;
+    c->committed = true;
+    return 0;
+}
+
+int rtb_scene_set(rtb_ctx *c, const RtbSceneDesc *s) {
+    if (!c || !s) return 1;
+    if (rtb_scene_begin(c) != 0) return 1;
+    for (int i = 0; i < s->num_images; i++)
+        if (rtb_scene_add_image(c, s->images[i].rgb, s->images[i].width, s->images[i].height) < 0) return fail(c, "rtb_scene_set", "bad image");
+    for (int i = 0; i < s->num_materials; i++) rtb_scene_add_material(c, &s->materials[i]);
+    for (int i = 0; i < s->num_objects; i++) {
+        RtbObject o = s->objects[i];
+        if (o.type == RTB_OBJ_MESH) {
+            if (o.tri_first < 0 || o.tri_count < 0 || o.tri_first + o.tri_count > s->num_mesh_tris) return fail(c, "rtb_scene_set", "mesh triangle range out of bounds");
+            const float *uv = s->mesh_tri_uv ? s->mesh_tri_uv + (size_t)o.tri_first * 6 : nullptr;
+            if (rtb_scene_add_mesh(c, s->mesh_tri_points + (size_t)o.tri_first * 9, uv, o.tri_count, o.material) < 0) return 1;
+        } else if (add_object(c, o) < 0) {
+            return 1;
+        }
+    }
+    return rtb_scene_commit(c);
+}
+
+int rtb_scene_desc(rtb_ctx *c, RtbSceneDesc *out) {
+    if (!c || !out) return 1;
+    out->num_objects = (int)c->objects.size(); out->objects = c->objects.data();
+    out->num_materials = (int)c->materials.size(); out->materials = c->materials.data();
+    out->num_mesh_tris = (int)(c->tri_points.size() / 9); out->mesh_tri_points = c->tri_points.data();
+    out->mesh_tri_uv = c->tri_uv.data();
+    out->num_images = (int)c->images.size(); out->images = c->images.data();
+    return 0;
+}
+
+static int fetch_counters(rtb_ctx *c) {
+    if (!c->opt_counters) return 0;
+    unsigned long long h[6];
+    RTB_CUDA(c, cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream), "reading counters");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "reading counters");
+    c->last_counters = RtbCounters{h[0], h[1], h[2], h[3], h[4], h[5]};
+    return 0;
+}
+
+int rtb_render(rtb_ctx *c, float *rgb_inout, int *frame_num_inout, int current_time_ms) {
+    if (!c || !rgb_inout || !frame_num_inout) return 1;
+    Bind b(c);
+    if (check_ready(c) != 0) return 1;
+    size_t bytes = c->image_floats * sizeof(float);
+    RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_inout, bytes, cudaMemcpyHostToDevice, c->stream), "copying previous render");
+    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream), "clearing counters");
+    RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
+    if (launch_frame(c, current_time_ms, *frame_num_inout) != 0) return 1;
+    RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "render");
+    RTB_CUDA(c, cudaMemcpyAsync(rgb_inout, c->d_image, bytes, cudaMemcpyDeviceToHost, c->stream), "copying image to host");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "final check after render");
+    c->timing_pending = true;
+    (*frame_num_inout)++;
+    c->frame_num = *frame_num_inout;
+    return fetch_counters(c);
+}
+
+int rtb_render_device(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) {
+    if (!c || n_frames < 0) return 1;
+    Bind b(c);
+    if (check_ready(c) != 0) return 1;
+    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream), "clearing counters");
+    RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
+    for (int k = 0; k < n_frames; k++) {
+        if (launch_frame(c, time0_ms + k * time_step_ms, c->frame_num) != 0) return 1;
+        c->frame_num++;
+    }
+    RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "render");
+    c->timing_pending = true;
+    return 0;
+}
+
+int rtb_sync(rtb_ctx *c) {
+    if (!c) return 1;
+    Bind b(c);
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "final check after render");
+    return fetch_counters(c);
+}
+
+int rtb_reset_accumulation(rtb_ctx *c) {
+    if (!c) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    RTB_CUDA(c, cudaMemsetAsync(c->d_image, 0, c->image_floats * sizeof(float), c->stream), "clearing image");
+    c->frame_num = 0;
+    return 0;
+}
+
+int rtb_set_accumulation(rtb_ctx *c, const float *rgb_host, int frame_num) {
+    if (!c || !rgb_host) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_host, c->image_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream), "copying previous render");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying previous render");
+    c->frame_num = frame_num;
+    return 0;
+}
+
+int rtb_download(rtb_ctx *c, float *rgb_host, int *frame_num_out) {
+    if (!c || !rgb_host) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    RTB_CUDA(c, cudaMemcpyAsync(rgb_host, c->d_image, c->image_floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream), "copying image to host");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying image to host");
+    if (frame_num_out) *frame_num_out = c->frame_num;
+    return 0;
+}
+
+void *rtb_device_image(rtb_ctx *c) {
+    if (!c) return nullptr;
+    Bind b(c);
+    if (ensure_image(c) != 0) return nullptr;
+    return c->d_image;
+}
+
+void *rtb_stream(rtb_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+int rtb_last_device_ms(rtb_ctx *c, float *ms_out) {
+    if (!c || !ms_out) return 1;
+    Bind b(c);
+    if (!c->timing_pending) return fail(c, "rtb_last_device_ms", "no timed render yet");
+    RTB_CUDA(c, cudaEventSynchronize(c->ev1), "timing");
+    RTB_CUDA(c, cudaEventElapsedTime(ms_out, c->ev0, c->ev1), "timing");
+    return 0;
+}
+
+int rtb_set_shard(rtb_ctx *c, int rank, int world, int band_rows) {
+    if (!c) return 1;
+    if (world < 1 || rank < 0 || rank >= world || band_rows < 1) return fail(c, "rtb_set_shard", "bad shard arguments");
+    c->shard_rank = rank; c->shard_world = world; c->band_rows = band_rows;
+    return 0;
+}
+
+int rtb_shard_rows(rtb_ctx *c, int *rows_this_rank, int *rows_padded) {
+    if (!c) return 1;
+    int mx = 0;
+    for (int r = 0; r < c->shard_world; r++) { int n = shard_local_rows(c, r); if (n > mx) mx = n; }
+    if (rows_this_rank) *rows_this_rank = shard_local_rows(c, c->shard_rank);
+    if (rows_padded) *rows_padded = mx;
+    return 0;
+}
+
+int rtb_shard_pack(rtb_ctx *c, void *dense_dev) {
+    if (!c || !dense_dev) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    int rows = shard_local_rows(c, c->shard_rank);
+    int n = rows * c->width * 3;
+    if (n > 0) shard_pack_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_image, (float *)dense_dev, c->width, rows, c->shard_rank, c->shard_world, c->band_rows, c->height);
+    RTB_CUDA(c, cudaGetLastError(), "packing shard");
+    return 0;
+}
+
+int rtb_shard_unpack(rtb_ctx *c, const void *gathered_dev) {
+    if (!c || !gathered_dev) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    int padded = 0;
+    rtb_shard_rows(c, nullptr, &padded);
+    size_t n = (size_t)padded * c->width * 3 * c->shard_world;
+    if (n > 0) shard_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_image, (const float *)gathered_dev, c->width, padded, c->shard_world, c->band_rows, c->height);
+    RTB_CUDA(c, cudaGetLastError(), "unpacking shards");
+    return 0;
+}
+
+int rtb_primary_ids(rtb_ctx *c, int32_t *obj_id, int32_t *sub_id, float *t) {
+    if (!c || !obj_id || !sub_id) return 1;
+    Bind b(c);
+    if (!c->have_cam) return fail(c, "rtb_primary_ids", "camera not set");
+    if (!c->committed) return fail(c, "rtb_primary_ids", "scene not committed");
+    size_t n = (size_t)c->width * c->height;
+    int32_t *d_obj = nullptr, *d_sub = nullptr;
+    float *d_t = nullptr;
+    RTB_CUDA(c, cudaMalloc((void **)&d_obj, n * 4), "allocating id buffers");
+    cudaError_t e = cudaMalloc((void **)&d_sub, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_t, n * 4);
+    if (e == cudaSuccess) {
+        IdsParams p;
+        p.scene = c->d;
+        std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
+        p.width = c->width; p.height = c->height;
+        p.obj_id = d_obj; p.sub_id = d_sub; p.t = d_t;
+        e = c->opt_strict ? strict::launch_primary_ids(p, c->opt_traversal == 1, c->stream) : fast::launch_primary_ids(p, c->opt_traversal == 1, c->stream);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(obj_id, d_obj, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sub_id, d_sub, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && t) e = cudaMemcpyAsync(t, d_t, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_obj); cudaFree(d_sub); cudaFree(d_t);
+    if (e != cudaSuccess) return fail(c, "rtb_primary_ids", cudaGetErrorString(e));
+    return 0;
+}
+
+int rtb_counters(rtb_ctx *c, RtbCounters *out) {
+    if (!c || !out) return 1;
+    *out = c->last_counters;
+    return 0;
+}
+
+int rtb_set_option(rtb_ctx *c, const char *key, int value) {
+    if (!c || !key) return 1;
+    std::string k(key);
+    if (k == "counters") c->opt_counters = value;
+    else if (k == "traversal") c->opt_traversal = value;
+    else if (k == "strict_fp") c->opt_strict = value;
+    else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
+    else if (k == "block_threads") {
+        if (value != RTB_BLOCK_THREADS) return fail(c, "rtb_set_option", "block_threads is fixed at build time");
+    } else if (k == "blocks_per_sm") c->opt_blocks_per_sm = value;
+    else return fail(c, "rtb_set_option", "unknown option");
+    return 0;
+}
+
+int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
+    if (!c || !key || !value) return 1;
+    std::string k(key);
+    if (k == "num_prims") *value = c->d.num_prims;
+    else if (k == "num_tris") *value = c->d.num_tris;
+    else if (k == "num_quads") *value = c->d.num_quads;
+    else if (k == "num_spheres") *value = c->d.num_spheres;
+    else if (k == "num_nodes") *value = c->d.num_prims > 1 ? c->d.num_prims - 1 : 0;
+    else if (k == "build_ms") *value = c->build_ms;
+    else if (k == "scene_bytes") *value = (double)c->scene_bytes;
+    else if (k == "culled_tris") *value = c->culled_tris;
+    else if (k == "num_sms") *value = c->num_sms;
+    else if (k == "block_threads") *value = c->opt_threads;
+    else if (k == "blocks_per_sm") {
+        int per_sm = c->opt_blocks_per_sm;
+        if (per_sm <= 0) { Bind b(c); (c->opt_strict ? strict::render_occupancy : fast::render_occupancy)(c->opt_threads, &per_sm); }
+        *value = per_sm;
+    } else if (k == "frame_num") *value = c->frame_num;
+    else return fail(c, "rtb_get_info", "unknown key");
+    return 0;
+}
+
+}  // extern "C"

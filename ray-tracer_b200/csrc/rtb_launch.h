@@ -1,0 +1,44 @@
+// rtb_launch.h -- kernel parameter blocks and the host-callable launchers each render variant
+// (fast: -fmad=true, strict: -fmad=false) exports.  Shared between rtb_api.cu and rtb_render_*.cu.
+#pragma once
+#include "rtb_device.cuh"
+
+namespace rtb {
+
+struct RenderParams {
+    DScene scene;
+    DCamera cam;
+    DRender rd;
+    int width, height;
+    int time_ms, frame_num;
+    const float *prev;  // previous running mean (may alias out)
+    float *out;
+    // screen-tile sharding: this launch renders rows y with (y / band_rows) % world == rank
+    int shard_rank, shard_world, band_rows;
+    int local_rows;                  // rows owned by this rank
+    unsigned int *work_counter;      // zeroed before launch
+    unsigned long long *counters;    // 6 slots (RtbCounters order) or nullptr
+};
+
+struct IdsParams {
+    DScene scene;
+    DCamera cam;
+    int width, height;
+    int32_t *obj_id, *sub_id;
+    float *t;
+};
+
+struct LaunchConfig {
+    int blocks, threads;
+};
+
+#define RTB_DECLARE_VARIANT(ns)                                                                                     \
+    namespace ns {                                                                                                  \
+    cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st);    \
+    cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st);                                \
+    cudaError_t render_occupancy(int threads, int *blocks_per_sm);                                                  \
+    }
+RTB_DECLARE_VARIANT(fast)
+RTB_DECLARE_VARIANT(strict)
+
+}  // namespace rtb

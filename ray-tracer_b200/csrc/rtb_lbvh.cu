@@ -1,0 +1,323 @@
+// rtb_lbvh.cu -- GPU LBVH build: primitive bounds -> 30-bit Morton codes -> stable LSD radix sort
+// -> Karras (2012) hierarchy -> bottom-up refit -> 64-byte two-child nodes.
+// Replaces the reference's host BVH constructor (src/objects.cu:452-464,602-770: recursive
+// median split by distance to a reference point, fixed depth 10, one cudaMalloc per node) and its
+// linear loop over objects (src/raytracer.cu:31): ONE tree over every primitive of the scene.
+// The tree shape is not parity surface; the traversal is conservative with respect to the exact
+// primitive tests (rtb_trace.cuh) and the tie rules are order independent.
+#include "rtb_lbvh.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtb {
+namespace {
+
+__device__ __forceinline__ unsigned int enc_float(float f) {
+    unsigned int b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float dec_float(unsigned int e) {
+    return __uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e);
+}
+
+__device__ __forceinline__ void grow(float3 &lo, float3 &hi, float x, float y, float z) {
+    lo.x = fminf(lo.x, x); lo.y = fminf(lo.y, y); lo.z = fminf(lo.z, z);
+    hi.x = fmaxf(hi.x, x); hi.y = fmaxf(hi.y, y); hi.z = fmaxf(hi.z, z);
+}
+
+__device__ __forceinline__ void grow_tri(float3 &lo, float3 &hi, const float4 *T) {
+    float4 a = T[0], b = T[1], c = T[2];
+    float3 p0 = make_float3(a.x, a.y, a.z), s1 = make_float3(a.w, b.x, b.y), s2 = make_float3(b.z, b.w, c.x);
+    grow(lo, hi, p0.x, p0.y, p0.z);
+    // p0 + side re-rounds the vertex; one ulp either way is covered by the box padding in pack_nodes
+    grow(lo, hi, p0.x + s1.x, p0.y + s1.y, p0.z + s1.z);
+    grow(lo, hi, p0.x + s2.x, p0.y + s2.y, p0.z + s2.z);
+}
+
+// K1: bounds of every leaf + scene bounds of the centroids
+__global__ void leaf_bounds_kernel(LbvhInput in, float4 *leaf_lo, float4 *leaf_hi, unsigned int *scene_bounds) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.num_prims) return;
+    int enc = ~in.leaf_refs[i], kind = enc & 3, idx = enc >> 2;
+    float3 lo = make_float3(3.0e38f, 3.0e38f, 3.0e38f), hi = make_float3(-3.0e38f, -3.0e38f, -3.0e38f);
+    if (kind == KIND_TRI) {
+        grow_tri(lo, hi, in.tris + 3 * idx);
+    } else if (kind == KIND_QUAD) {
+        grow_tri(lo, hi, in.quads + 7 * idx);
+        grow_tri(lo, hi, in.quads + 7 * idx + 3);
+    } else {
+        float4 s = in.spheres[idx];
+        float r = fabsf(s.w) * 1.000001f;
+        grow(lo, hi, s.x - r, s.y - r, s.z - r);
+        grow(lo, hi, s.x + r, s.y + r, s.z + r);
+    }
+    leaf_lo[i] = make_float4(lo.x, lo.y, lo.z, 0.f);
+    leaf_hi[i] = make_float4(hi.x, hi.y, hi.z, 0.f);
+    float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+    atomicMin(scene_bounds + 0, enc_float(cx)); atomicMin(scene_bounds + 1, enc_float(cy)); atomicMin(scene_bounds + 2, enc_float(cz));
+    atomicMax(scene_bounds + 3, enc_float(cx)); atomicMax(scene_bounds + 4, enc_float(cy)); atomicMax(scene_bounds + 5, enc_float(cz));
+}
+
+__device__ __forceinline__ unsigned int expand_bits(unsigned int v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+// K2: 30-bit Morton code of the leaf centroid
+__global__ void morton_kernel(int n, const float4 *leaf_lo, const float4 *leaf_hi, const unsigned int *scene_bounds,
+                              unsigned int *keys, int *vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 mn = make_float3(dec_float(scene_bounds[0]), dec_float(scene_bounds[1]), dec_float(scene_bounds[2]));
+    float3 mx = make_float3(dec_float(scene_bounds[3]), dec_float(scene_bounds[4]), dec_float(scene_bounds[5]));
+    float4 lo = leaf_lo[i], hi = leaf_hi[i];
+    float ex = fmaxf(mx.x - mn.x, 1e-30f), ey = fmaxf(mx.y - mn.y, 1e-30f), ez = fmaxf(mx.z - mn.z, 1e-30f);
+    float x = (0.5f * (lo.x + hi.x) - mn.x) / ex, y = (0.5f * (lo.y + hi.y) - mn.y) / ey, z = (0.5f * (lo.z + hi.z) - mn.z) / ez;
+    unsigned int xi = (unsigned int)fminf(fmaxf(x * 1024.f, 0.f), 1023.f);
+    unsigned int yi = (unsigned int)fminf(fmaxf(y * 1024.f, 0.f), 1023.f);
+    unsigned int zi = (unsigned int)fminf(fmaxf(z * 1024.f, 0.f), 1023.f);
+    keys[i] = (expand_bits(xi) << 2) | (expand_bits(yi) << 1) | expand_bits(zi);
+    vals[i] = i;
+}
+
+// ---- stable LSD radix sort, 8 bits per pass ------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 8;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+
+__global__ void sort_hist_kernel(int n, const unsigned int *keys, int shift, unsigned int *block_hist, int num_blocks) {
+    __shared__ unsigned int hist[256];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * SORT_TILE;
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        int i = base + k * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&hist[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    block_hist[threadIdx.x * num_blocks + blockIdx.x] = hist[threadIdx.x];  // digit-major
+}
+
+// exclusive scan of the digit-major histogram by ONE block (<= a few hundred thousand entries)
+__global__ void sort_scan_kernel(unsigned int *data, int n) {
+    __shared__ unsigned int warp_sums[32];
+    __shared__ unsigned int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += blockDim.x) {
+        int i = base + threadIdx.x;
+        unsigned int v = i < n ? data[i] : 0, x = v;
+        int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sums[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int w = lane < (int)(blockDim.x >> 5) ? warp_sums[lane] : 0, ws = w;
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned int y = __shfl_up_sync(0xffffffffu, ws, o);
+                if (lane >= o) ws += y;
+            }
+            warp_sums[lane] = ws - w;  // exclusive
+        }
+        __syncthreads();
+        unsigned int excl = carry + warp_sums[warp] + (x - v);
+        if (i < n) data[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = excl + v;
+        __syncthreads();
+    }
+}
+
+__global__ void sort_scatter_kernel(int n, const unsigned int *keys_in, const int *vals_in, unsigned int *keys_out, int *vals_out,
+                                    int shift, const unsigned int *block_offsets, int num_blocks) {
+    __shared__ unsigned int next_pos[256];  // next output slot of this block for each digit
+    next_pos[threadIdx.x] = block_offsets[threadIdx.x * num_blocks + blockIdx.x];
+    __syncthreads();
+    int base = blockIdx.x * SORT_TILE;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        int i = base + k * SORT_THREADS + threadIdx.x;
+        bool valid = i < n;
+        unsigned int key = valid ? keys_in[i] : 0xffffffffu;
+        unsigned int digit = (key >> shift) & 255u;
+        // stable rank: warps take their turn in order, lanes in order inside a warp
+        unsigned int peers = __match_any_sync(0xffffffffu, valid ? digit : 256u);
+        unsigned int rank = __popc(peers & ((1u << lane) - 1u));
+        int leader = __ffs(peers) - 1;
+        unsigned int pos = 0;
+        for (int w = 0; w < SORT_THREADS / 32; w++) {
+            if (warp == w && valid) {
+                unsigned int start = 0;
+                if (lane == leader) {
+                    start = next_pos[digit];
+                    next_pos[digit] = start + __popc(peers);
+                }
+                start = __shfl_sync(peers, start, leader);
+                pos = start + rank;
+            }
+            __syncthreads();
+        }
+        if (valid) {
+            keys_out[pos] = key;
+            vals_out[pos] = vals_in[i];
+        }
+    }
+}
+
+// ---- Karras 2012 ---------------------------------------------------------------------------------
+__device__ __forceinline__ int delta(const unsigned int *keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    unsigned int a = keys[i], b = keys[j];
+    if (a != b) return __clz(a ^ b);
+    return 32 + __clz((unsigned int)i ^ (unsigned int)j);  // duplicate codes: fall back to the position
+}
+
+// child encoding during the build: >= 0 internal node, < 0 leaf ~sorted_position
+__global__ void karras_kernel(int n, const unsigned int *keys, int2 *children, int *parent_internal, int *parent_leaf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    int gamma = i + s * d + min(d, 0);
+    int left = (min(i, j) == gamma) ? ~gamma : gamma;
+    int right = (max(i, j) == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    children[i] = make_int2(left, right);
+    if (left >= 0) parent_internal[left] = i; else parent_leaf[~left] = i;
+    if (right >= 0) parent_internal[right] = i; else parent_leaf[~right] = i;
+    if (i == 0) parent_internal[0] = -1;
+}
+
+// bottom-up refit: the second thread to reach a node owns it
+__global__ void refit_kernel(int n, const int *vals, const float4 *leaf_lo, const float4 *leaf_hi, const int2 *children,
+                             const int *parent_internal, const int *parent_leaf, float4 *node_lo, float4 *node_hi, int *flags) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int node = parent_leaf[i];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[node], 1) == 0) return;
+        __threadfence();
+        int2 c = children[node];
+        float4 l0, h0, l1, h1;
+        if (c.x >= 0) { l0 = __ldcg(node_lo + c.x); h0 = __ldcg(node_hi + c.x); } else { l0 = leaf_lo[vals[~c.x]]; h0 = leaf_hi[vals[~c.x]]; }
+        if (c.y >= 0) { l1 = __ldcg(node_lo + c.y); h1 = __ldcg(node_hi + c.y); } else { l1 = leaf_lo[vals[~c.y]]; h1 = leaf_hi[vals[~c.y]]; }
+        __stcg(node_lo + node, make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f));
+        __stcg(node_hi + node, make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.f));
+        node = parent_internal[node];
+    }
+}
+
+__device__ __forceinline__ void padded(float4 lo, float4 hi, int ref, float4 &olo, float4 &ohi) {
+    float px = 4e-7f * fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), hi.x - lo.x) + 1e-12f;
+    float py = 4e-7f * fmaxf(fmaxf(fabsf(lo.y), fabsf(hi.y)), hi.y - lo.y) + 1e-12f;
+    float pz = 4e-7f * fmaxf(fmaxf(fabsf(lo.z), fabsf(hi.z)), hi.z - lo.z) + 1e-12f;
+    olo = make_float4(lo.x - px, lo.y - py, lo.z - pz, __int_as_float(ref));
+    ohi = make_float4(hi.x + px, hi.y + py, hi.z + pz, 0.f);
+}
+
+// final layout: node i = {lo0.xyz, ref0} {hi0.xyz, -} {lo1.xyz, ref1} {hi1.xyz, -}
+__global__ void pack_nodes_kernel(int n, const int *vals, const int *leaf_refs, const float4 *leaf_lo, const float4 *leaf_hi,
+                                  const int2 *children, const float4 *node_lo, const float4 *node_hi, float4 *nodes) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 c = children[i];
+    float4 lo, hi, olo, ohi;
+    int ref;
+    if (c.x >= 0) { lo = node_lo[c.x]; hi = node_hi[c.x]; ref = c.x; } else { int v = vals[~c.x]; lo = leaf_lo[v]; hi = leaf_hi[v]; ref = leaf_refs[v]; }
+    padded(lo, hi, ref, olo, ohi);
+    nodes[4 * i] = olo; nodes[4 * i + 1] = ohi;
+    if (c.y >= 0) { lo = node_lo[c.y]; hi = node_hi[c.y]; ref = c.y; } else { int v = vals[~c.y]; lo = leaf_lo[v]; hi = leaf_hi[v]; ref = leaf_refs[v]; }
+    padded(lo, hi, ref, olo, ohi);
+    nodes[4 * i + 2] = olo; nodes[4 * i + 3] = ohi;
+}
+
+__global__ void init_bounds_kernel(unsigned int *b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 0xffffffffu;
+    else if (threadIdx.x < 6) b[threadIdx.x] = 0u;
+}
+
+}  // namespace
+
+#define LBVH_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
+
+cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st) {
+    *nodes_out = nullptr;
+    *root_ref = 0;
+    const int n = in.num_prims;
+    if (n <= 0) return cudaSuccess;
+    if (n == 1) {
+        int ref;
+        cudaError_t e = cudaMemcpyAsync(&ref, in.leaf_refs, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+        e = cudaStreamSynchronize(st);
+        *root_ref = ref;
+        return e;
+    }
+    cudaError_t err = cudaSuccess;
+    const int T = 256, B = (n + T - 1) / T;
+    const int sort_blocks = (n + SORT_TILE - 1) / SORT_TILE;
+    float4 *leaf_lo = nullptr, *leaf_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr, *nodes = nullptr;
+    unsigned int *keys = nullptr, *keys2 = nullptr, *hist = nullptr, *bounds = nullptr;
+    int *vals = nullptr, *vals2 = nullptr, *parent_internal = nullptr, *parent_leaf = nullptr, *flags = nullptr;
+    int2 *children = nullptr;
+    LBVH_CHECK(cudaMalloc(&leaf_lo, sizeof(float4) * n));
+    LBVH_CHECK(cudaMalloc(&leaf_hi, sizeof(float4) * n));
+    LBVH_CHECK(cudaMalloc(&node_lo, sizeof(float4) * n));
+    LBVH_CHECK(cudaMalloc(&node_hi, sizeof(float4) * n));
+    LBVH_CHECK(cudaMalloc(&nodes, sizeof(float4) * 4 * (size_t)(n - 1)));
+    LBVH_CHECK(cudaMalloc(&keys, sizeof(unsigned int) * n));
+    LBVH_CHECK(cudaMalloc(&keys2, sizeof(unsigned int) * n));
+    LBVH_CHECK(cudaMalloc(&vals, sizeof(int) * n));
+    LBVH_CHECK(cudaMalloc(&vals2, sizeof(int) * n));
+    LBVH_CHECK(cudaMalloc(&hist, sizeof(unsigned int) * 256 * (size_t)sort_blocks));
+    LBVH_CHECK(cudaMalloc(&bounds, sizeof(unsigned int) * 6));
+    LBVH_CHECK(cudaMalloc(&parent_internal, sizeof(int) * n));
+    LBVH_CHECK(cudaMalloc(&parent_leaf, sizeof(int) * n));
+    LBVH_CHECK(cudaMalloc(&flags, sizeof(int) * n));
+    LBVH_CHECK(cudaMalloc(&children, sizeof(int2) * n));
+    LBVH_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * n, st));
+
+    init_bounds_kernel<<<1, 32, 0, st>>>(bounds);
+    leaf_bounds_kernel<<<B, T, 0, st>>>(in, leaf_lo, leaf_hi, bounds);
+    morton_kernel<<<B, T, 0, st>>>(n, leaf_lo, leaf_hi, bounds, keys, vals);
+    for (int shift = 0; shift < 32; shift += 8) {
+        sort_hist_kernel<<<sort_blocks, SORT_THREADS, 0, st>>>(n, keys, shift, hist, sort_blocks);
+        sort_scan_kernel<<<1, 1024, 0, st>>>(hist, 256 * sort_blocks);
+        sort_scatter_kernel<<<sort_blocks, SORT_THREADS, 0, st>>>(n, keys, vals, keys2, vals2, shift, hist, sort_blocks);
+        unsigned int *tk = keys; keys = keys2; keys2 = tk;
+        int *tv = vals; vals = vals2; vals2 = tv;
+    }
+    karras_kernel<<<B, T, 0, st>>>(n, keys, children, parent_internal, parent_leaf);
+    refit_kernel<<<B, T, 0, st>>>(n, vals, leaf_lo, leaf_hi, children, parent_internal, parent_leaf, node_lo, node_hi, flags);
+    pack_nodes_kernel<<<B, T, 0, st>>>(n, vals, in.leaf_refs, leaf_lo, leaf_hi, children, node_lo, node_hi, nodes);
+    LBVH_CHECK(cudaGetLastError());
+    LBVH_CHECK(cudaStreamSynchronize(st));
+    *nodes_out = nodes;
+    nodes = nullptr;
+    *root_ref = 0;
+done:
+    cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(node_lo); cudaFree(node_hi); cudaFree(nodes);
+    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2); cudaFree(hist); cudaFree(bounds);
+    cudaFree(parent_internal); cudaFree(parent_leaf); cudaFree(flags); cudaFree(children);
+    return err;
+}
+
+}  // namespace rtb

@@ -1,0 +1,19 @@
+// rtb_lbvh.h -- GPU LBVH builder interface (see rtb_lbvh.cu)
+#pragma once
+#include "rtb_device.cuh"
+
+namespace rtb {
+
+struct LbvhInput {
+    int num_prims;
+    const int *leaf_refs;    // device: encoded leaf refs (~((index << 2) | kind)), creation order
+    const float4 *tris;      // device primitive records (layout in rtb_device.cuh)
+    const float4 *quads;
+    const float4 *spheres;
+};
+
+// Builds the tree on `st`.  *nodes_out: cudaMalloc'd (n-1)*4 float4 (caller frees), nullptr when n < 2.
+// *root_ref: 0 (internal node 0) or, for a single primitive, its leaf ref.
+cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st);
+
+}  // namespace rtb

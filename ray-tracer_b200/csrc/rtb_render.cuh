@@ -1,0 +1,332 @@
+// rtb_render.cuh -- the render kernels.  Included by rtb_render_fast.cu (default -fmad=true, like
+// the reference's own nvcc build) and rtb_render_strict.cu (-fmad=false: + - * / sqrt round exactly
+// as written, which makes primary-hit ids and distances bit-identical to the host oracle).
+// RTB_NS names the variant's namespace.
+#pragma once
+#include "rtb_trace.cuh"
+#include "rtb_launch.h"
+
+namespace rtb {
+namespace RTB_NS {
+
+// float(3.141592653589793), camera.cu:9
+#define RTB_PI_F 3.14159274101257324f
+
+struct Surface {
+    V3 point, normal;
+    float u, v;
+    int material;
+};
+
+// RayHitData of the winning primitive (objects.cu:55-68,154-160) + the object's material index
+__device__ __forceinline__ void make_surface(const DScene &s, const Ray &r, const Best &b, Surface &sf) {
+    int kind = b.code & 3, idx = b.code >> 3;
+    sf.point = r.d * b.t + r.o;  // Ray::get_pos, ray.cu:63-65
+    sf.u = 0; sf.v = 0;
+    int obj;
+    if (kind == KIND_SPHERE) {
+        float4 sp = __ldg(s.spheres + idx);
+        V3 c = v3(sp.x, sp.y, sp.z);
+        sf.normal = normalised(sf.point - c);
+        obj = __ldg(s.sphere_ids + idx);
+        sf.material = __ldg(s.obj_material + obj);
+        if (__ldg(&s.materials[sf.material].need_uv)) {  // assign_texture_coords, objects.cu:82-97
+            float theta = asinf((sf.point.y - c.y) / sp.w);
+            float phi = acosf((sf.point.x - c.x) / sp.w);
+            float u = (theta + RTB_PI_F / 2) / RTB_PI_F;
+            float v_ratio = (1 - phi / RTB_PI_F) / 2;
+            int behind = sf.point.z > c.z;
+            int mult = 1 - 2 * behind;
+            sf.u = u;
+            sf.v = 1 * behind + mult * v_ratio;
+        }
+        return;
+    }
+    const float4 *T;
+    if (kind == KIND_TRI) {
+        T = s.tris + 3 * idx;
+        obj = __ldg(s.tri_ids + idx).x;
+    } else {
+        T = s.quads + 7 * idx + 3 * ((b.code >> 2) & 1);
+        obj = __ldg(s.quad_ids + idx).x;
+    }
+    float4 c = __ldg(T + 2);
+    V3 n = v3(c.y, c.z, c.w);
+    sf.normal = n * (float)(1 - 2 * (dot(n, r.d) > 0));  // objects.cu:158
+    sf.material = __ldg(s.obj_material + obj);
+    if (__ldg(&s.materials[sf.material].need_uv)) {
+        // assign_texture_coords(hit, w, u, v): tp0*w + tp1*u + tp2*v, objects.cu:160,196-199
+        float w = 1 - b.u - b.v;
+        float2 t0, t1, t2;
+        if (kind == KIND_TRI) {
+            t0 = __ldg(s.tri_uv + 3 * idx); t1 = __ldg(s.tri_uv + 3 * idx + 1); t2 = __ldg(s.tri_uv + 3 * idx + 2);
+        } else if ((b.code >> 2) & 1) {  // Quad::create_triangles, objects.cu:246-252
+            t0 = make_float2(0, 0); t1 = make_float2(0, 1); t2 = make_float2(1, 1);
+        } else {
+            t0 = make_float2(0, 0); t1 = make_float2(1, 0); t2 = make_float2(1, 1);
+        }
+        sf.u = (t0.x * w + t1.x * b.u) + t2.x * b.v;
+        sf.v = (t0.y * w + t1.y * b.u) + t2.y * b.v;
+    }
+}
+
+__device__ __forceinline__ void change_direction(Ray &r, V3 d) {  // ray.cu:198-202
+    r.d = d;
+    r.inv = v3(1 / d.x, 1 / d.y, 1 / d.z);
+}
+
+// Ray::apply_antialias, ray.cu:130-142: (u - 0.5) * 2 * RANGE in double, RANGE = float(0.001)
+__device__ __forceinline__ void apply_antialias(Ray &r, uint32_t &rng) {
+    const double range = (double)0.001f;
+    V3 off;
+    off.x = (float)(((double)rng_next(rng) - 0.5) * 2 * range);
+    off.y = (float)(((double)rng_next(rng) - 0.5) * 2 * range);
+    off.z = (float)(((double)rng_next(rng) - 0.5) * 2 * range);
+    change_direction(r, normalised(r.d + off));
+}
+
+// Ray::reflect, ray.cu:67-75 with diffuse_reflect :157-170, true_lambertian_reflect :172-178,
+// perfect_reflect :180-186, lerp :32-34
+__device__ __forceinline__ void reflect(Ray &r, const Surface &sf, float smoothness, uint32_t &rng) {
+    float dx = rng_normal(rng);
+    float dy = rng_normal(rng);
+    float dz = rng_normal(rng);
+    V3 rv = v3(dx, dy, dz);
+    if (dot(rv, sf.normal) < 0) rv = rv * -1.f;
+    rv = normalised(rv);
+    V3 diffuse = normalised(sf.normal + rv);
+    float dn = dot(r.d, sf.normal);
+    V3 spec = normalised(r.d - sf.normal * 2.f * dn);
+    r.o = sf.point;
+    change_direction(r, normalised(diffuse + (spec - diffuse) * smoothness));
+}
+
+// Ray::refract, ray.cu:77-128 + get_reflection_coeff :188-196
+static __device__ __noinline__ void refract(Ray &r, const Surface &sf, float mat_n, float smoothness, float &cur_n, uint32_t &rng) {
+    float n1, n2;
+    V3 refn;
+    if (dot(sf.normal, r.d) > 0) {
+        n1 = mat_n; n2 = cur_n; refn = sf.normal;
+    } else {
+        n1 = cur_n; n2 = mat_n; refn = sf.normal * -1.f;
+    }
+    cur_n = n2;
+    float theta1 = acos(min(dot(r.d, refn), 1.0));           // double overloads, as in the reference
+    float theta2 = asin(min(n1 * sin(theta1) / n2, 1.0));
+    float critical = asin(n2 / n1);
+    float sqrt_r0 = (n1 - n2) / (n1 + n2);
+    float r0 = sqrt_r0 * sqrt_r0;
+    float cos_theta = cos(theta1);
+    float coeff = r0 + (1 - r0) * pow((1 - cos_theta), 5);
+    if (theta1 > critical || coeff > rng_next(rng)) {
+        reflect(r, sf, smoothness, rng);
+        return;
+    }
+    V3 perp;
+    if (theta1 != 0) perp = (r.d - refn * cos(theta1)) / sin(theta1);
+    else perp = v3(0, 0, 0);
+    V3 res = refn * cos(theta2) + perp * sin(theta2);
+    r.o = sf.point;
+    change_direction(r, normalised(res));
+}
+
+// Texture::get_texture_colour, material.cu:53-124
+__device__ __forceinline__ V3 texture_colour(const DScene &s, const DMaterial &m, float u, float v) {
+    switch (m.tex_type) {
+        case 0: return v3(m.a[0], m.a[1], m.a[2]);
+        case 1: return v3(u, v, 0);
+        case 2: {
+            int uc = u * m.num_squares;
+            int vc = v * m.num_squares;
+            if ((uc + vc) % 2 == 0) return v3(m.a[0], m.a[1], m.a[2]);
+            return v3(m.b[0], m.b[1], m.b[2]);
+        }
+        case 3: {
+            int uc = (m.img_w - 1) * u;
+            int vc = (m.img_h - 1) * v;
+            int idx = vc * m.img_w + uc;
+            idx = max(0, min(idx, m.img_w * m.img_h - 1));  // the reference reads out of bounds here
+            const float *px = s.image_rgb + m.img_offset + 3 * idx;
+            return v3(__ldg(px), __ldg(px + 1), __ldg(px + 2));
+        }
+    }
+    return v3(0, 0, 0);
+}
+
+// cam_pixel_to_world (camera.cu:24-29) + Ray::set_direction_origin (ray.cu:147-155)
+__device__ __forceinline__ V3 primary_direction(const DCamera &c, int x, int y) {
+    V3 du = v3(c.du[0], c.du[1], c.du[2]), dv = v3(c.dv[0], c.dv[1], c.dv[2]);
+    V3 plane_point = du * (float)x + dv * (float)y;
+    V3 view_pos = v3(c.tl[0], c.tl[1], c.tl[2]) + plane_point;
+    V3 o = v3(c.cam_pos[0], c.cam_pos[1], c.cam_pos[2]);
+    return normalised(view_pos - o);
+}
+
+template <bool BRUTE> __device__ __forceinline__ Best trace(const DScene &s, const Ray &r, Counters &cnt) {
+    if (BRUTE) return trace_brute(s, r, cnt);
+    return trace_bvh(s, r, cnt);
+}
+
+// local row index -> global row for the row-cyclic band sharding (SURVEY.md 8(e) partitioning A)
+__device__ __forceinline__ int shard_row(const RenderParams &p, int local_row) {
+    if (p.shard_world <= 1) return local_row;
+    int band = local_row / p.band_rows, within = local_row - band * p.band_rows;
+    return (band * p.shard_world + p.shard_rank) * p.band_rows + within;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Persistent megakernel.  One lane owns one pixel at a time and runs the reference's per-pixel
+// function (get_pixel_colour -> get_ray_colour -> trace_ray, raytracer.cu:67-136) as a state
+// machine whose unit of work is ONE SEGMENT, so that all 32 lanes of a warp are inside the
+// traversal together no matter which sample / bounce each is at.  The samples of a pixel stay
+// serial in their lane because the RNG state is per pixel and carried from sample to sample
+// (SURVEY.md F10/H1).  Pixels are handed out in 8x4 tiles through one atomic counter.
+// ---------------------------------------------------------------------------------------------
+template <bool BRUTE, bool COUNT>
+__global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_megakernel(const RenderParams p) {
+    const DScene &s = p.scene;
+    const int spp = p.rd.rays_per_pixel, limit = p.rd.reflection_limit;
+    const bool aa = p.rd.antialias != 0;
+    const V3 sky = v3(p.rd.sky[0], p.rd.sky[1], p.rd.sky[2]);
+    const V3 cam_o = v3(p.cam.cam_pos[0], p.cam.cam_pos[1], p.cam.cam_pos[2]);
+    const int tiles_x = (p.width + 7) >> 3, tiles_y = (p.local_rows + 3) >> 2;
+    const unsigned int total = (unsigned int)tiles_x * tiles_y * 32u;
+
+    Counters cnt;
+    unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
+#ifdef RTB_COUNTERS
+    cnt.box = cnt.tri = cnt.sph = 0;
+#endif
+
+    int array_index = -1;  // (y * W + x) * 3 of the pixel this lane owns, -1 = none
+    uint32_t rng = 0;
+    int sample = 0, bounce = 0;
+    V3 pdir = v3(0, 0, 1);
+    Ray ray;
+    ray.o = cam_o; ray.d = pdir; ray.inv = pdir;
+    V3 thr = v3(1, 1, 1), col = v3(0, 0, 0), acc = v3(0, 0, 0);
+    float cur_n = 1;
+
+    for (;;) {
+        if (array_index < 0) {
+            unsigned int idx = atomicAdd(p.work_counter, 1u);
+            if (idx >= total) break;
+            unsigned int tile = idx >> 5, within = idx & 31u;
+            int x = (int)(tile % tiles_x) * 8 + (int)(within & 7u);
+            int ly = (int)(tile / tiles_x) * 4 + (int)(within >> 3);
+            if (x >= p.width || ly >= p.local_rows) continue;
+            int y = shard_row(p, ly);
+            if (y >= p.height) continue;
+            array_index = (y * p.width + x) * 3;  // raytracer.cu:123
+            rng = rng_seed(array_index, p.time_ms);
+            pdir = primary_direction(p.cam, x, y);
+            acc = v3(0, 0, 0);
+            sample = 0;
+            bounce = 0;
+        }
+        if (bounce == 0) {
+            if (sample >= spp) {
+                // get_ray_colour, raytracer.cu:107-112
+                V3 colour = acc / (float)spp;
+                V3 previous = v3(p.prev[array_index], p.prev[array_index + 1], p.prev[array_index + 2]);
+                V3 previous_sum = previous * (float)p.frame_num;
+                V3 res = (colour + previous_sum) / (float)(p.frame_num + 1);
+                p.out[array_index] = res.x;
+                p.out[array_index + 1] = res.y;
+                p.out[array_index + 2] = res.z;
+                array_index = -1;
+                continue;
+            }
+            // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
+            ray.o = cam_o;
+            change_direction(ray, pdir);
+            cur_n = 1;
+            thr = v3(1, 1, 1);
+            col = v3(0, 0, 0);
+            if (COUNT) n_samples++;
+            if (limit <= 0) { sample++; continue; }
+        }
+        // ---- one segment: raytracer.cu:70-91 ----
+        if (aa) apply_antialias(ray, rng);
+        Best best = trace<BRUTE>(s, ray, cnt);
+        if (COUNT) n_seg++;
+        bool end_sample;
+        if (best.code < 0) {
+            col = col + sky * thr;
+            end_sample = true;
+        } else {
+            if (COUNT) n_hit++;
+            Surface sf;
+            make_surface(s, ray, best, sf);
+            const DMaterial &m = s.materials[sf.material];
+            int mtype = __ldg(&m.type);
+            if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), cur_n, rng);
+            else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), rng);
+            if (mtype == 1) col = col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * thr;
+            else thr = thr * texture_colour(s, m, sf.u, sf.v);
+            bounce++;
+            end_sample = bounce >= limit;
+        }
+        if (end_sample) {
+            acc = acc + col;
+            sample++;
+            bounce = 0;
+        }
+    }
+    if (COUNT && p.counters) {
+        atomicAdd(p.counters + 0, n_seg);
+        atomicAdd(p.counters + 1, n_hit);
+#ifdef RTB_COUNTERS
+        atomicAdd(p.counters + 2, cnt.box);
+        atomicAdd(p.counters + 3, cnt.tri);
+        atomicAdd(p.counters + 4, cnt.sph);
+#endif
+        atomicAdd(p.counters + 5, n_samples);
+    }
+}
+
+// primary-hit ids, antialias off; one thread per pixel
+template <bool BRUTE> __global__ void primary_ids_kernel(const IdsParams p) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= p.width || y >= p.height) return;
+    Ray ray;
+    ray.o = v3(p.cam.cam_pos[0], p.cam.cam_pos[1], p.cam.cam_pos[2]);
+    change_direction(ray, primary_direction(p.cam, x, y));
+    Counters cnt;
+#ifdef RTB_COUNTERS
+    cnt.box = cnt.tri = cnt.sph = 0;
+#endif
+    Best best = trace<BRUTE>(p.scene, ray, cnt);
+    size_t i = (size_t)y * p.width + x;
+    if (best.code < 0) {
+        p.obj_id[i] = -1; p.sub_id[i] = -1; p.t[i] = RTB_INF_F;
+    } else {
+        int2 ids = code_ids(p.scene, best.code);
+        p.obj_id[i] = ids.x; p.sub_id[i] = ids.y; p.t[i] = best.t;
+    }
+}
+
+cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st) {
+    if (brute) {
+        if (count) render_megakernel<true, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        else render_megakernel<true, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+    } else {
+        if (count) render_megakernel<false, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        else render_megakernel<false, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st) {
+    dim3 block(8, 8), grid((p.width + 7) / 8, (p.height + 7) / 8);
+    if (brute) primary_ids_kernel<true><<<grid, block, 0, st>>>(p);
+    else primary_ids_kernel<false><<<grid, block, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t render_occupancy(int threads, int *blocks_per_sm) {
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_megakernel<false, false>, threads, 0);
+}
+
+}  // namespace RTB_NS
+}  // namespace rtb

@@ -1,0 +1,113 @@
+"""TEST INFRASTRUCTURE: ctypes bindings of the two checkers.
+
+  Oracle  -> oracle/libpt_oracle.so   (plain-C restatement, always buildable)
+  RefHost -> oracle/_ref/libref_host.so (the reference's own source compiled for the host; built only
+             where /root/reference exists, travels to the GPU box as a binary)
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg import this module.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+import raytracer_b200 as rtb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_ORACLE = os.path.join(ROOT, "oracle", "libpt_oracle.so")
+_REF = os.path.join(ROOT, "oracle", "_ref", "libref_host.so")
+NTHREADS = max(1, min(os.cpu_count() or 1, 32))
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+class Oracle:
+    lib = None
+
+    def __init__(self, scene):
+        if Oracle.lib is None:
+            L = ctypes.CDLL(_ORACLE)
+            L.pto_scene_create.restype = ctypes.c_void_p
+            L.pto_scene_create.argtypes = [ctypes.POINTER(rtb.SceneDesc)]
+            L.pto_scene_destroy.argtypes = [ctypes.c_void_p]
+            L.pto_render.argtypes = [ctypes.c_void_p, ctypes.POINTER(rtb.CamData), ctypes.c_int, ctypes.c_int,
+                                     ctypes.POINTER(rtb.RenderData), ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(rtb.Counters)]
+            L.pto_primary_ids.argtypes = [ctypes.c_void_p, ctypes.POINTER(rtb.CamData), ctypes.c_int, ctypes.c_int,
+                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+            L.pto_seed.restype = ctypes.c_uint
+            L.pto_rng.restype = ctypes.c_float
+            L.pto_rng.argtypes = [ctypes.POINTER(ctypes.c_uint)]
+            L.pto_normal.restype = ctypes.c_float
+            L.pto_normal.argtypes = [ctypes.POINTER(ctypes.c_uint)]
+            L.pto_default_camera.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(rtb.CamData)]
+            L.pto_primary_dir.argtypes = [ctypes.POINTER(rtb.CamData), ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+            Oracle.lib = L
+        desc = scene.desc if isinstance(scene, rtb.Scene) else scene
+        self._keep = scene
+        self.scene = Oracle.lib.pto_scene_create(ctypes.byref(desc))
+
+    def __del__(self):
+        if getattr(self, "scene", None):
+            Oracle.lib.pto_scene_destroy(self.scene)
+            self.scene = None
+
+    def render(self, cam, w, h, rd, time_ms, frame_num, prev, y0=0, y1=None, nthreads=NTHREADS, counters=None):
+        out = np.zeros((h, w, 3), np.float32)
+        if prev is not None:
+            prev = np.ascontiguousarray(prev, np.float32)
+        Oracle.lib.pto_render(self.scene, ctypes.byref(cam), w, h, ctypes.byref(rd), time_ms, frame_num, _p(prev), _p(out),
+                              y0, h if y1 is None else y1, nthreads, ctypes.byref(counters) if counters is not None else None)
+        return out
+
+    def primary_ids(self, cam, w, h, nthreads=NTHREADS):
+        obj, sub, t = np.empty((h, w), np.int32), np.empty((h, w), np.int32), np.empty((h, w), np.float32)
+        Oracle.lib.pto_primary_ids(self.scene, ctypes.byref(cam), w, h, _p(obj), _p(sub), _p(t), nthreads)
+        return obj, sub, t
+
+
+def have_ref_host():
+    return os.path.exists(_REF)
+
+
+class RefHost:
+    """The reference's own source on the host.  Process-global state (like the reference's
+    __constant__ symbols): one scene at a time."""
+    lib = None
+
+    def __init__(self):
+        if RefHost.lib is None:
+            L = ctypes.CDLL(_REF)
+            L.refh_last_error.restype = ctypes.c_char_p
+            L.refh_seed.restype = ctypes.c_uint
+            L.refh_normal.restype = ctypes.c_float
+            L.refh_rng_value.restype = ctypes.c_float
+            L.refh_set_render.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_float]
+            RefHost.lib = L
+        self.L = RefHost.lib
+
+    def build_scene(self, scene_id, p0=0, p1=0, from_main=False):
+        rc = self.L.refh_build_scene(scene_id, p0, p1, rtb.models_dir().encode(), int(from_main))
+        if rc != 0:
+            raise RuntimeError(self.L.refh_last_error().decode())
+
+    def set_render(self, rd):
+        self.L.refh_set_render(rd.rays_per_pixel, rd.reflection_limit, rd.antialias, rd.sky_colour.x, rd.sky_colour.y, rd.sky_colour.z)
+
+    def set_camera(self, w, h):
+        cam = (ctypes.c_float * 12)()
+        self.L.refh_set_camera(w, h, cam)
+        return np.array(cam, np.float32)
+
+    def render(self, w, h, time_ms, frame_num, prev, nthreads=NTHREADS):
+        out = np.zeros((h, w, 3), np.float32)
+        if prev is not None:
+            prev = np.ascontiguousarray(prev, np.float32)
+        self.L.refh_render(w, h, 0, h, time_ms, frame_num, _p(prev), _p(out), nthreads)
+        return out
+
+    def primary_ids(self, w, h, nthreads=NTHREADS):
+        obj, sub, t = np.empty((h, w), np.int32), np.empty((h, w), np.int32), np.empty((h, w), np.float32)
+        self.L.refh_primary_ids(w, h, _p(obj), _p(sub), _p(t), nthreads)
+        return obj, sub, t
