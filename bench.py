@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark: Mrays/s (and 1080p spp/s) of the per-pixel path-tracing hot
+path on N B200s, measured on the workload BASELINE.json quotes its target on.
+
+    python bench.py --gpus N --steps K --warmup W [--workload C3] [--impl reference]
+
+A "step" is one frame (one pass of the hot path over every pixel: spp x bounces segments).
+Workloads:  C1 1000x800/100spp/5b scene 0 | C2 1080p/64/8 cube+spheres |
+C3 1080p/256/8 Cornell+monkey (DEFAULT: the config the >=20x target is quoted on) |
+C4 4K/1024/8 1M-triangle grid (spp bounded per step) | C5 = C3 geometry at 4K, sample slices.
+
+value  = Mrays/s, device-timed (CUDA events on the render stream), scene and accumulation buffer
+         resident in HBM; whole job (all ranks), time = max over ranks.
+e2e    = the same metric through the reference-facing entry point rtb_render() == render(
+         VariableRenderData*, int): host image in, host image out, H2D and D2H inside the timed region.
+N > 1  : one process per GPU (torchrun), row-cyclic band sharding of the SAME frame (strong scaling,
+         image identical to 1 GPU), NCCL all-gather of the bands inside the timed region.
+--impl reference : the reference's OWN CUDA build (baseline/_ref, unmodified sources, resolution
+         constants patched) on the same workload at a bounded spp per step (a rate, spp independent);
+         if that library is absent, the reference source on the host cores (oracle/_ref), else the C port.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    #        scene p0 p1   W     H    spp  bounces
+    "C1": (0, 0, 0, 1000, 800, 100, 5),
+    "C2": (5, 0, 0, 1920, 1080, 64, 8),
+    "C3": (0, 0, 0, 1920, 1080, 256, 8),
+    "C4": (6, 40, 35, 3840, 2160, 16, 8),   # 1024 spp in the config; 16 spp per step keeps a step ~1 s
+    "C5": (0, 0, 0, 3840, 2160, 128, 8),
+}
+WORKLOAD_DESC = {
+    "C1": "reference default scene 0 (Cornell box + Suzanne 723 tris + mirror sphere) 1000x800 100spp 5 bounces",
+    "C2": "cube.obj (12 tris) + spheres 1920x1080 64spp 8 bounces",
+    "C3": "low_poly_monkey.obj scene (Cornell box + Suzanne + sphere) 1920x1080 256spp 8 bounces",
+    "C4": "1,012,200-triangle monkey grid 3840x2160 8 bounces, 16 spp per step (of 1024)",
+    "C5": "scene 0 geometry 3840x2160 8 bounces, 128 spp per step (progressive to 16384)",
+}
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.proc = None
+        self.lines = []
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(power), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def flops_per_ray(c):
+    """canonical cost of the reference's formulas, weighted by the measured op mix."""
+    seg = max(1, c["segments"])
+    return (24.0 * c["box_tests"] + 48.0 * c["tri_tests"] + 30.0 * c["sphere_tests"] + 250.0 * c["hit_segments"]) / seg + 40.0
+
+
+def bytes_per_ray(c):
+    seg = max(1, c["segments"])
+    return (32.0 * c["box_tests"] + 48.0 * c["tri_tests"] + 16.0 * c["sphere_tests"]) / seg
+
+
+def cpu_baseline_leg(workload, threads):
+    """The reference's own source on the host cores (oracle/_ref), else the C port: a bounded band of
+    the same workload at 1 spp.  Returns the cpu_baseline object."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes
+    import numpy as np
+    import oracle_binding as ob
+    import raytracer_b200 as rtb
+    sid, p0, p1, W, H, spp, bounces = WORKLOADS[workload]
+    if sid == 6:
+        p0, p1 = 6, 5  # the host BVH of the full grid takes minutes to build; a 6x5 grid is the sample
+    # 8 bands of H/128 rows spread evenly over the frame (1/16 of the pixels)
+    nb, band = 8, max(1, H // 128)
+    bands = [((2 * b + 1) * H // (2 * nb) - band // 2, (2 * b + 1) * H // (2 * nb) - band // 2 + band) for b in range(nb)]
+    scene = rtb.Scene(sid, p0, p1)
+    rd = scene.render_settings(1, bounces)
+    rays, dt = 0, 0.0
+    if ob.have_ref_host():
+        ref = ob.RefHost()
+        ref.build_scene(sid, p0, p1)
+        ref.set_render(rd)
+        ref.set_camera(W, H)
+        out = np.zeros((H, W, 3), np.float32)
+        for y0, y1 in bands:
+            t0 = time.perf_counter()
+            ref.L.refh_render(W, H, y0, y1, 12345, 0, None, out.ctypes.data_as(ctypes.c_void_p), threads)
+            dt += time.perf_counter() - t0
+            seg, hits = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+            ref.L.refh_count_segments(W, H, y0, y1, 12345, ctypes.byref(seg), ctypes.byref(hits), os.cpu_count() or 1)
+            rays += seg.value
+        kind = "reference"
+    else:
+        orc = ob.Oracle(scene)
+        for y0, y1 in bands:
+            cnt = rtb.Counters()
+            t0 = time.perf_counter()
+            orc.render(rtb.default_camera(W, H), W, H, rd, 12345, 0, None, y0=y0, y1=y1, nthreads=threads, counters=cnt)
+            dt += time.perf_counter() - t0
+            rays += cnt.segments
+        kind = "port"
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
+            "sample": f"{workload} scene at {W}x{H}, {nb} bands of {band} rows spread over the frame, 1 spp, {bounces} bounces: {rays} rays in {dt:.2f} s"
+                      + (" (6x5 instance grid)" if sid == 6 else "")}
+
+
+def reference_arm(args):
+    """--impl reference.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import oracle_binding as ob
+    sid, p0, p1, W, H, spp, bounces = WORKLOADS[args.workload]
+    base = {"impl": "reference", "metric": "Mrays/s", "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic"}
+    threads = os.cpu_count() or 1
+    if os.path.exists(ob.ref_cuda_path(W, H)):
+        import raytracer_b200 as rtb
+        # rays per frame from our counter build at the bounded spp (identical inputs, untimed)
+        ref_spp = args.ref_spp
+        scene = rtb.Scene(sid, p0, p1)
+        tr = rtb.Tracer(0).setup(scene, W, H, ref_spp, bounces)
+        tr.set_option("counters", 1)
+        tr.render_device(1, 1000)
+        tr.sync()
+        rays = tr.counters()["segments"]
+        tr.close()
+        ref = ob.RefCuda(W, H)
+        ref.init(sid, p0, p1, ref_spp, bounces, True)
+        img = np.zeros((H, W, 3), np.float32)
+        sampler = ClockSampler(0)
+        for k in range(args.warmup):
+            ref.render_kernel(img, 0, 900 + k)
+        sampler.start()
+        kernel_ms = [ref.render_kernel(img, 0, 1000 + k) for k in range(args.steps)]
+        clocks = sampler.stop()
+        # end to end through the reference's own render() (src/dispatch.cu:156): wall clock
+        frame, wall = 0, []
+        img2 = np.zeros((H, W, 3), np.float32)
+        ref.render(img2, 0, 899)
+        for k in range(args.steps):
+            frame, ms = ref.render(img2, 0, 1000 + k)
+            wall.append(ms)
+        ms_step = sum(kernel_ms) / len(kernel_ms)
+        value = rays / ms_step / 1e3
+        e2e = rays / (sum(wall) / len(wall)) / 1e3
+        nbytes = W * H * 3 * 4
+        line = dict(base, value=value, ms_per_step=ms_step, clocks=clocks, gpu_launches=args.steps,
+                    spp_per_s_1080p=(ref_spp / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
+                    e2e={"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes + 8, "d2h_bytes_per_step": nbytes,
+                         "note": "reference render(): per-frame cudaMalloc + H2D of previous_render, managed-memory read-back"},
+                    config={"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "reference_build": "the reference's own CUDA kernel get_pixel_colour, nvcc -arch=sm_100, default flags",
+                            "spp_per_step": ref_spp, "rays_per_step": rays, "note": "Mrays/s is a rate: spp per step is bounded so that a step stays ~1-3 s",
+                            "l2": "working set is L2-resident by design; see DESIGN.md"},
+                    cpu_baseline=cpu_baseline_leg(args.workload, threads))
+    else:
+        cb = cpu_baseline_leg(args.workload, threads)
+        line = dict(base, value=cb["value"], ms_per_step=None, cpu_baseline=cb, gpu_launches=0,
+                    e2e={"value": cb["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    config={"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "reference_build": "reference CUDA library absent; host build of the reference source"})
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="rtb")
+    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--band-rows", type=int, default=8)
+    ap.add_argument("--ref-spp", type=int, default=8, help="spp per step of the reference arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import numpy as np
+    import torch
+    import raytracer_b200 as rtb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the render path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    sid, p0, p1, W, H, spp, bounces = WORKLOADS[args.workload]
+    scene = rtb.Scene(sid, p0, p1)
+    tr = rtb.Tracer(local_rank).setup(scene, W, H, spp, bounces)
+    if world > 1:
+        tr.set_shard(rank, world, args.band_rows)
+    ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
+    rows_mine, rows_pad = tr.shard_rows()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(ext):
+        dense = gathered = None
+        if world > 1:
+            dense = torch.zeros(rows_pad * W * 3, device="cuda", dtype=torch.float32)
+            gathered = torch.empty(world * rows_pad * W * 3, device="cuda", dtype=torch.float32)
+
+        def device_step(k):
+            """one frame, everything resident: render my bands (+ pack, all-gather, unpack)"""
+            tr.reset()
+            tr.render_device(1, 1000 + k)
+            n = 1
+            if world > 1:
+                tr.shard_pack(dense.data_ptr())
+                dist.all_gather_into_tensor(gathered, dense)
+                tr.shard_unpack(gathered.data_ptr())
+                n += 2
+            return n
+
+        # op mix / ray count of one step: counter build, same inputs, untimed
+        tr.set_option("counters", 1)
+        tr.reset()
+        tr.render_device(1, 1000)
+        tr.sync()
+        cnt = tr.counters()
+        tr.set_option("counters", 0)
+        t = torch.tensor([float(cnt[k]) for k in ("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples")],
+                         device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(t)
+        cnt = dict(zip(("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples"), [int(x) for x in t.tolist()]))
+        rays_per_step = cnt["segments"]
+
+        for k in range(args.warmup):
+            device_step(k)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        launches = 0
+        ev0.record(ext)
+        for k in range(args.steps):
+            kev[k][0].record(ext)
+            tr.reset()
+            tr.render_device(1, 1000 + k)
+            kev[k][1].record(ext)
+            launches += 1
+            if world > 1:
+                tr.shard_pack(dense.data_ptr())
+                dist.all_gather_into_tensor(gathered, dense)
+                tr.shard_unpack(gathered.data_ptr())
+                launches += 2
+        ev1.record(ext)
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms_total = ev0.elapsed_time(ev1)
+        kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+        tt = torch.tensor([ms_total, kernel_ms], device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total, kernel_ms = tt.tolist()
+
+        # ---- end to end through the reference-facing entry point, host buffers ----
+        host = torch.zeros(H * W * 3, dtype=torch.float32).pin_memory()
+        himg = host.numpy()
+        nbytes = H * W * 3 * 4
+
+        def e2e_step(k):
+            if world == 1:
+                himg[:] = 0  # the caller's previous_render (frame 0)
+                tr.render(himg, 0, 1000 + k)  # H2D + kernel + D2H + sync
+            else:
+                tr.set_accumulation(himg, 0)  # H2D
+                tr.render_device(1, 1000 + k)
+                tr.shard_pack(dense.data_ptr())
+                dist.all_gather_into_tensor(gathered, dense)
+                tr.shard_unpack(gathered.data_ptr())
+                out, _ = tr.download()  # D2H + sync
+                himg[:] = out.reshape(-1)
+
+        e2e_step(0)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            e2e_step(k)
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        te = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_ms = te.item()
+        checksum = float(himg.astype(np.float64).sum())
+        fp32_peak = tr.fp32_peak_tflops(40.0) if rank == 0 else None
+
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        value = rays_per_step / ms_step / 1e3                       # Mrays/s, whole job
+        e2e_value = rays_per_step / (e2e_ms / args.steps) / 1e3
+        fpr = flops_per_ray(cnt)
+        peaks = load_peaks()
+        nominal_peak = 148 * 128 * 2 * (peaks["sm_max_mhz"] if peaks else 1965.0) * 1e6 / 1e12
+        kernel_rate = rays_per_step / world / kernel_ms / 1e3      # Mrays/s of ONE launch on one GPU
+        achieved_tf = kernel_rate * 1e6 * fpr / 1e12
+        hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+        achieved_gbs = (kernel_rate * 1e6 * bytes_per_ray(cnt) + (W * H // world) * 24 / (kernel_ms / 1e3)) / 1e9
+        line = {
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "spp_per_s_1080p": (spp / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
+            "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "scene_id": sid, "width": W, "height": H, "spp_per_step": spp,
+                       "bounces": bounces, "rays_per_step": rays_per_step, "segments_per_sample": cnt["segments"] / max(1, cnt["samples"]),
+                       "sharding": "none" if world == 1 else f"row-cyclic bands of {args.band_rows} rows, NCCL all-gather per frame",
+                       "kernel": "persistent megakernel, LBVH", "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
+                       "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
+                    "ms_per_step": e2e_ms / args.steps, "checksum": checksum},
+            "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak if fp32_peak else None,
+                         "peak_kind": "measured FFMA microbenchmark on this GPU (rtb_measure_fp32_peak)", "peak_nominal": nominal_peak,
+                         "frac_of_nominal": achieved_tf / nominal_peak, "traffic": None,
+                         "flops_per_ray": fpr, "kernel_ms": kernel_ms,
+                         "op_mix_per_ray": {"box": cnt["box_tests"] / cnt["segments"], "tri": cnt["tri_tests"] / cnt["segments"],
+                                            "sphere": cnt["sphere_tests"] / cnt["segments"], "hit": cnt["hit_segments"] / cnt["segments"]},
+                         "why": "no dense contraction and an L2-resident working set: the FP32 pipe bounds this path (SURVEY.md 8(d))",
+                         "hbm": {"achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                                 "peak_kind": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"}},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_leg(args.workload, 1)
+        print(json.dumps(line), flush=True)
+    tr.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

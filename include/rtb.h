@@ -202,6 +202,9 @@ int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
  * "kernel" 0 = persistent megakernel, 1 = wavefront; "block_threads"; "blocks_per_sm" */
 int rtb_set_option(rtb_ctx *ctx, const char *key, int value);
 int rtb_get_info(rtb_ctx *ctx, const char *key, double *value);
+/* sustained FP32 FMA throughput of the device (TFLOP/s, dependent-chain FFMA microbenchmark over
+ * `ms_target` milliseconds): the measured denominator of the FP32 roofline */
+int rtb_measure_fp32_peak(rtb_ctx *ctx, double ms_target, double *tflops_out);
 
 #ifdef __cplusplus
 }

@@ -294,9 +294,10 @@ int refh_primary_ids(int w, int h, int32_t *obj_id, int32_t *sub_id, float *t_ou
 }
 
 // segments ("rays") and hit segments of one frame, for the Mrays/s denominator
-int refh_count_segments(int w, int h, int time_ms, unsigned long long *segments, unsigned long long *hits, int nthreads) {
+int refh_count_segments(int w, int h, int y0, int y1, int time_ms, unsigned long long *segments, unsigned long long *hits, int nthreads) {
     std::vector<SegCount> rows(h);
-    parallel_rows(h, nthreads, [&](int y) {
+    parallel_rows(y1 - y0, nthreads, [&](int yy) {
+        int y = y0 + yy;
         for (int x = 0; x < w; x++) {
             int array_index = (y * w + x) * 3;
             uint rng_state = array_index * 3145739 + time_ms * 6291469;

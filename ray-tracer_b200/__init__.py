@@ -130,6 +130,7 @@ lib.rtb_primary_ids.argtypes = [_vp, _vp, _vp, _vp]
 lib.rtb_counters.argtypes = [_vp, ctypes.POINTER(Counters)]
 lib.rtb_set_option.argtypes = [_vp, ctypes.c_char_p, _i]
 lib.rtb_get_info.argtypes = [_vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
+lib.rtb_measure_fp32_peak.argtypes = [_vp, ctypes.c_double, ctypes.POINTER(ctypes.c_double)]
 
 scenes_lib.rtbs_build.restype = _vp
 scenes_lib.rtbs_build.argtypes = [_i, _i, _i, ctypes.c_char_p]
@@ -299,6 +300,11 @@ class Tracer:
         self._check(lib.rtb_primary_ids(self.ctx, _ptr(obj), _ptr(sub), _ptr(t)))
         shape = (self.height, self.width)
         return obj.reshape(shape), sub.reshape(shape), t.reshape(shape)
+
+    def fp32_peak_tflops(self, ms_target=50.0):
+        v = ctypes.c_double()
+        self._check(lib.rtb_measure_fp32_peak(self.ctx, ms_target, ctypes.byref(v)))
+        return v.value
 
     def counters(self):
         c = Counters()

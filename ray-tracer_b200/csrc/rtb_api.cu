@@ -346,6 +346,22 @@ int check_ready(rtb_ctx *c) {
 
 }  // namespace
 
+namespace {
+// 8 independent FFMA chains per thread; 2 flop per FFMA
+__global__ void fma_peak_kernel(float *out, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 12345.678f) out[0] = s;
+}
+}  // namespace
+
 // ======================================= extern "C" ==================================================
 extern "C" {
 
@@ -752,6 +768,33 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
         if (value != RTB_BLOCK_THREADS) return fail(c, "rtb_set_option", "block_threads is fixed at build time");
     } else if (k == "blocks_per_sm") c->opt_blocks_per_sm = value;
     else return fail(c, "rtb_set_option", "unknown option");
+    return 0;
+}
+
+int rtb_measure_fp32_peak(rtb_ctx *c, double ms_target, double *tflops_out) {
+    if (!c || !tflops_out) return 1;
+    Bind b(c);
+    float *d = nullptr;
+    RTB_CUDA(c, cudaMalloc((void **)&d, 4), "fp32 peak");
+    const int threads = 256, blocks = c->num_sms * 8;
+    int iters = 2000;
+    float ms = 0;
+    double best = 0;
+    for (int rep = 0; rep < 6; rep++) {
+        cudaEventRecord(c->ev0, c->stream);
+        fma_peak_kernel<<<blocks, threads, 0, c->stream>>>(d, iters, 0.999f, 0.001f);
+        cudaEventRecord(c->ev1, c->stream);
+        cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { cudaFree(d); return fail(c, "fp32 peak", cudaGetErrorString(e)); }
+        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        double flops = 2.0 * 8 * 16 * (double)iters * threads * blocks;
+        double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+        if (ms < ms_target && iters < (1 << 24)) iters = (int)(iters * (ms_target / (ms > 0.01f ? ms : 0.01f)) * 1.1) + 1;
+    }
+    cudaFree(d);
+    c->timing_pending = false;
+    *tflops_out = best;
     return 0;
 }
 

@@ -111,3 +111,50 @@ class RefHost:
         obj, sub, t = np.empty((h, w), np.int32), np.empty((h, w), np.int32), np.empty((h, w), np.float32)
         self.L.refh_primary_ids(w, h, _p(obj), _p(sub), _p(t), nthreads)
         return obj, sub, t
+
+
+def ref_cuda_path(w, h):
+    return os.path.join(ROOT, "baseline", "_ref", f"libref_cuda_{w}x{h}.so")
+
+
+class RefCuda:
+    """The reference's own CUDA build (baseline/ref_cuda.cu), one library per resolution.
+    Process-global state (its three __constant__ symbols)."""
+    _libs = {}
+
+    def __init__(self, w, h):
+        path = ref_cuda_path(w, h)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        if (w, h) not in RefCuda._libs:
+            L = ctypes.CDLL(path)
+            L.refc_last_error.restype = ctypes.c_char_p
+            L.refc_init.argtypes = [ctypes.c_int] * 3 + [ctypes.c_char_p] + [ctypes.c_int] * 3
+            RefCuda._libs[(w, h)] = L
+        self.L = RefCuda._libs[(w, h)]
+        self.w, self.h = w, h
+        assert self.L.refc_width() == w and self.L.refc_height() == h
+
+    def init(self, scene_id, p0, p1, spp, bounces, antialias=True):
+        if self.L.refc_init(scene_id, p0, p1, rtb.models_dir().encode(), spp, bounces, int(antialias)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+
+    def render_kernel(self, image, frame_num, time_ms):
+        """kernel-only device time (ms); image in/out like render()"""
+        ms = ctypes.c_float()
+        if self.L.refc_render_kernel(_p(image), frame_num, time_ms, ctypes.byref(ms)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+        return ms.value
+
+    def render(self, image, frame_num, time_ms):
+        """the reference's own render(): returns (new frame_num, wall ms)"""
+        f, ms = ctypes.c_int(frame_num), ctypes.c_double()
+        if self.L.refc_render(_p(image), ctypes.byref(f), time_ms, ctypes.byref(ms)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+        return f.value, ms.value
+
+    def primary_ids(self):
+        obj, t = np.empty((self.h, self.w), np.int32), np.empty((self.h, self.w), np.float32)
+        if self.L.refc_primary_ids(_p(obj), _p(t)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+        return obj, t

@@ -1,0 +1,61 @@
+"""GPU parity against the reference's OWN CUDA build (baseline/_ref/libref_cuda_320x256.so, built
+here from the unmodified reference sources with only the resolution constants patched): the strict
+comparison the north_star names.  Skipped when the prebuilt library is absent."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+import raytracer_b200 as rtb
+
+pytestmark = pytest.mark.gpu
+W, H = 320, 256
+needs_ref = pytest.mark.skipif(not os.path.exists(ob.ref_cuda_path(W, H)), reason="reference CUDA build not present")
+
+SCENES = [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 0, 0), (4, 60, 7), (5, 0, 0), (6, 4, 3)]
+
+
+@needs_ref
+@pytest.mark.parametrize("sid,p0,p1", SCENES)
+def test_ids_and_radiance_vs_reference_cuda(sid, p0, p1):
+    spp, bounces = 8, 5
+    ref = ob.RefCuda(W, H)
+    ref.init(sid, p0, p1, spp, bounces, True)
+    r_obj, r_t = ref.primary_ids()
+    r_img = np.zeros((H, W, 3), np.float32)
+    ref.render_kernel(r_img, 0, 12345)
+    r_img2 = r_img.copy()
+    ref.render_kernel(r_img2, 1, 777)
+
+    scene = rtb.Scene(sid, p0, p1)
+    tr = rtb.Tracer(0).setup(scene, W, H, spp, bounces)
+    obj, sub, t = tr.primary_ids()
+    img = np.zeros((H, W, 3), np.float32)
+    tr.render(img, 0, 12345)
+    img2 = img.copy()
+    tr.render(img2, 1, 777)
+    tr.close()
+
+    mism = int((obj != r_obj).sum())
+    rmse = float(np.sqrt(((img - r_img) ** 2).mean()))
+    rmse2 = float(np.sqrt(((img2 - r_img2) ** 2).mean()))
+    ident = float((img == r_img).mean())
+    print(f"scene {sid}: id mismatches {mism}/{W*H}, t bit-equal {float((t == r_t).mean()):.6f}, "
+          f"RMSE {rmse:.3e} / frame1 {rmse2:.3e}, bit-identical floats {ident:.4f}")
+    # bit-exact ids for identical camera rays (north_star); the default-flag builds of both sides
+    # contract FMAs, so a few silhouette pixels may still differ -- measured and bounded
+    assert mism <= W * H // 2000, f"{mism} id mismatches vs the reference CUDA build"
+    assert rmse < 1e-3 and rmse2 < 1e-3
+
+
+@needs_ref
+def test_reference_render_entry_point_matches_its_kernel():
+    """render() (src/dispatch.cu:156) and the harness launch of the same kernel agree bit for bit."""
+    ref = ob.RefCuda(W, H)
+    ref.init(1, 0, 0, 2, 5, True)
+    a = np.zeros((H, W, 3), np.float32)
+    b = np.zeros((H, W, 3), np.float32)
+    ref.render_kernel(a, 0, 42)
+    f, _ = ref.render(b, 0, 42)
+    assert f == 1 and (a == b).all()
