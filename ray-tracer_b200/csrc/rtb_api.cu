@@ -11,7 +11,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <utility>
 #include <vector>
 
 using namespace rtb;
@@ -57,7 +59,7 @@ struct rtb_ctx {
     bool timing_pending = false;
 
     // options
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1;
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 12;
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
 };
@@ -135,35 +137,64 @@ TriRec make_tri(H3 p0, H3 p1, H3 p2) {
 }
 
 struct Flat {
-    std::vector<float4> tris, quads, spheres, ref_nodes;
-    std::vector<int2> tri_ids, quad_ids;
+    std::vector<float4> tris, spheres, ref_nodes;
+    std::vector<int2> tri_ids;
     std::vector<float2> tri_uv;
     std::vector<int> tri_refleaf, sphere_ids, obj_material, leaf_refs;
     std::vector<DMaterial> materials;
     std::vector<float> image_rgb;
+    std::vector<float> leaf_area;  // surface area of each leaf's bounding box (parallel to leaf_refs)
+    std::vector<float> leaf_box;   // lo.xyz hi.xyz of each leaf (parallel to leaf_refs)
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};  // scene bounds
     int culled = 0;
 
-    void add_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
+    void note_box(const float *blo, const float *bhi) {
+        float e[3];
+        for (int c = 0; c < 3; c++) {
+            e[c] = bhi[c] - blo[c];
+            if (blo[c] < lo[c]) lo[c] = blo[c];
+            if (bhi[c] > hi[c]) hi[c] = bhi[c];
+        }
+        leaf_area.push_back(2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]));
+        for (int c = 0; c < 3; c++) leaf_box.push_back(blo[c]);
+        for (int c = 0; c < 3; c++) leaf_box.push_back(bhi[c]);
+    }
+    void tri_box(int idx, int count, float *blo, float *bhi) const {
+        for (int c = 0; c < 3; c++) { blo[c] = 3e38f; bhi[c] = -3e38f; }
+        for (int k = 0; k < count; k++) {
+            float4 a = tris[3 * (idx + k)], b = tris[3 * (idx + k) + 1], cc = tris[3 * (idx + k) + 2];
+            float p[3][3] = {{a.x, a.y, a.z}, {a.x + a.w, a.y + b.x, a.z + b.y}, {a.x + b.z, a.y + b.w, a.z + cc.x}};
+            for (int v = 0; v < 3; v++)
+                for (int c = 0; c < 3; c++) { blo[c] = fminf(blo[c], p[v][c]); bhi[c] = fmaxf(bhi[c], p[v][c]); }
+        }
+    }
+
+    int push_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
         int idx = (int)tri_ids.size();
         tris.push_back(t.a); tris.push_back(t.b); tris.push_back(t.c);
         tri_ids.push_back(make_int2(obj, sub));
         for (int k = 0; k < 3; k++) tri_uv.push_back(uv ? make_float2(uv[2 * k], uv[2 * k + 1]) : make_float2(0, 0));
         tri_refleaf.push_back(refleaf);
-        leaf_refs.push_back(~((idx << 2) | KIND_TRI));
+        return idx;
     }
-    // Quad::create_triangles (objects.cu:244-253): t1 = (p1,p2,p3), t2 = (p1,p4,p3)
+    void add_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
+        int idx = push_tri(t, obj, sub, uv, refleaf);
+        leaf_refs.push_back(~((idx << RTB_KIND_BITS) | KIND_TRI));
+        float blo[3], bhi[3];
+        tri_box(idx, 1, blo, bhi);
+        note_box(blo, bhi);
+    }
+    // Quad::create_triangles (objects.cu:244-253): t1 = (p1,p2,p3) uv (0,0)(1,0)(1,1), t2 = (p1,p4,p3) uv (0,0)(0,1)(1,1).
+    // OneWayQuad's normal is +-t1.normal (objects.cu:285-289): carried by the leaf kind.
     void add_quad(H3 p1, H3 p2, H3 p3, H3 p4, int obj, int sub, bool one_way, bool invert) {
-        int idx = (int)quad_ids.size();
-        TriRec A = make_tri(p1, p2, p3), B = make_tri(p1, p4, p3);
-        quads.push_back(A.a); quads.push_back(A.b); quads.push_back(A.c);
-        quads.push_back(B.a); quads.push_back(B.b); quads.push_back(B.c);
-        float m = (float)(1 - 2 * (invert ? 1 : 0));  // OneWayQuad::get_normal_vec, objects.cu:285-289
-        float4 ow = make_float4(A.normal.x * m, A.normal.y * m, A.normal.z * m, 0.f);
-        int flag = one_way ? 1 : 0;
-        std::memcpy(&ow.w, &flag, sizeof(int));
-        quads.push_back(ow);
-        quad_ids.push_back(make_int2(obj, sub));
-        leaf_refs.push_back(~((idx << 2) | KIND_QUAD));
+        static const float uv1[6] = {0, 0, 1, 0, 1, 1}, uv2[6] = {0, 0, 0, 1, 1, 1};
+        int idx = push_tri(make_tri(p1, p2, p3), obj, sub, uv1, -1);
+        push_tri(make_tri(p1, p4, p3), obj, sub + 1, uv2, -1);
+        int kind = one_way ? (invert ? KIND_QUAD_ONEWAY_INV : KIND_QUAD_ONEWAY) : KIND_QUAD;
+        leaf_refs.push_back(~((idx << RTB_KIND_BITS) | kind));
+        float blo[3], bhi[3];
+        tri_box(idx, 2, blo, bhi);
+        note_box(blo, bhi);
     }
 };
 
@@ -207,7 +238,10 @@ int flatten(rtb_ctx *c, Flat &f) {
                 int idx = (int)f.sphere_ids.size();
                 f.spheres.push_back(make_float4(o.p[0].x, o.p[0].y, o.p[0].z, o.f[0]));
                 f.sphere_ids.push_back(i);
-                f.leaf_refs.push_back(~((idx << 2) | KIND_SPHERE));
+                f.leaf_refs.push_back(~((idx << RTB_KIND_BITS) | KIND_SPHERE));
+                float r = fabsf(o.f[0]);
+                float blo[3] = {o.p[0].x - r, o.p[0].y - r, o.p[0].z - r}, bhi[3] = {o.p[0].x + r, o.p[0].y + r, o.p[0].z + r};
+                f.note_box(blo, bhi);
                 break;
             }
             case RTB_OBJ_TRIANGLE: f.add_tri(make_tri(h3(o.p[0]), h3(o.p[1]), h3(o.p[2])), i, 0, o.uv, -1); break;
@@ -319,6 +353,7 @@ int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     p.prev = c->d_image; p.out = c->d_image;
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
+    p.refill = c->opt_refill < 1 ? 1 : (c->opt_refill > 32 ? 32 : c->opt_refill);
     p.work_counter = c->d_work;
     p.counters = c->opt_counters ? c->d_counters : nullptr;
     RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
@@ -519,8 +554,6 @@ int rtb_scene_commit(rtb_ctx *c) {
     RTB_CUDA(c, upload(c, f.tri_ids, &d.tri_ids), "uploading triangle ids");
     RTB_CUDA(c, upload(c, f.tri_uv, &d.tri_uv), "uploading triangle uvs");
     RTB_CUDA(c, upload(c, f.tri_refleaf, &d.tri_refleaf), "uploading reference leaves");
-    RTB_CUDA(c, upload(c, f.quads, &d.quads), "uploading quads");
-    RTB_CUDA(c, upload(c, f.quad_ids, &d.quad_ids), "uploading quad ids");
     RTB_CUDA(c, upload(c, f.spheres, &d.spheres), "uploading spheres");
     RTB_CUDA(c, upload(c, f.sphere_ids, &d.sphere_ids), "uploading sphere ids");
     RTB_CUDA(c, upload(c, f.obj_material, &d.obj_material), "uploading object materials");
@@ -529,16 +562,56 @@ int rtb_scene_commit(rtb_ctx *c) {
     RTB_CUDA(c, upload(c, f.ref_nodes, &d.ref_nodes), "uploading reference boxes");
     RTB_CUDA(c, upload(c, f.leaf_refs, &d.all_refs), "uploading primitive list");
     d.num_prims = (int)f.leaf_refs.size();
+    // large-primitive split: a leaf whose box area exceeds 1/20 of the scene box's is tested in the
+    // warp-uniform list instead of living in the tree (at most RTB_MAX_LARGE, the largest first)
+    std::vector<int> large, small;
+    if (c->opt_large_split && !f.leaf_refs.empty()) {
+        float e[3] = {f.hi[0] - f.lo[0], f.hi[1] - f.lo[1], f.hi[2] - f.lo[2]};
+        float scene_area = 2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
+        std::vector<std::pair<float, int>> cand;
+        for (size_t i = 0; i < f.leaf_refs.size(); i++)
+            if (f.leaf_area[i] > 0.05f * scene_area) cand.push_back({-f.leaf_area[i], (int)i});
+        std::sort(cand.begin(), cand.end());
+        if ((int)cand.size() > c->opt_max_large) cand.resize(c->opt_max_large);
+        std::vector<char> is_large(f.leaf_refs.size(), 0);
+        for (auto &pr : cand) is_large[pr.second] = 1;
+        for (size_t i = 0; i < f.leaf_refs.size(); i++) (is_large[i] ? large : small).push_back(f.leaf_refs[i]);
+    } else {
+        small = f.leaf_refs;
+    }
+    const int *d_small = nullptr;
+    // padded boxes of the large primitives (conservative pre-test before the exact one)
+    std::vector<float4> large_boxes;
+    {
+        std::vector<int> pos(f.leaf_refs.size());
+        size_t li = 0;
+        for (size_t i = 0; i < f.leaf_refs.size() && li < large.size(); i++) {
+            if (f.leaf_refs[i] != large[li]) continue;
+            const float *b = &f.leaf_box[6 * i];
+            float lo[3], hi[3];
+            for (int k = 0; k < 3; k++) {
+                float pad = 4e-7f * fmaxf(fmaxf(fabsf(b[k]), fabsf(b[3 + k])), b[3 + k] - b[k]) + 1e-12f;
+                lo[k] = b[k] - pad; hi[k] = b[3 + k] + pad;
+            }
+            large_boxes.push_back(make_float4(lo[0], lo[1], lo[2], 0.f));
+            large_boxes.push_back(make_float4(hi[0], hi[1], hi[2], 0.f));
+            li++;
+        }
+    }
+    RTB_CUDA(c, upload(c, large_boxes, &d.large_boxes), "uploading large-primitive boxes");
+    RTB_CUDA(c, upload(c, large, &d.large_refs), "uploading large-primitive list");
+    RTB_CUDA(c, upload(c, small, &d_small), "uploading tree primitive list");
+    d.num_large = (int)large.size();
+    d.num_bvh_prims = (int)small.size();
     d.num_tris = (int)f.tri_ids.size();
-    d.num_quads = (int)f.quad_ids.size();
     d.num_spheres = (int)f.sphere_ids.size();
     d.num_objects = (int)c->objects.size();
     c->culled_tris = f.culled;
 
     LbvhInput in;
-    in.num_prims = d.num_prims;
-    in.leaf_refs = d.all_refs;
-    in.tris = d.tris; in.quads = d.quads; in.spheres = d.spheres;
+    in.num_prims = d.num_bvh_prims;
+    in.leaf_refs = d_small;
+    in.tris = d.tris; in.spheres = d.spheres;
     float4 *nodes = nullptr;
     int root = 0;
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "timing LBVH build");
@@ -550,7 +623,7 @@ int rtb_scene_commit(rtb_ctx *c) {
     c->build_ms = ms;
     if (nodes) {
         c->scene_allocs.push_back(nodes);
-        c->scene_bytes += sizeof(float4) * 4 * (size_t)(d.num_prims - 1);
+        c->scene_bytes += sizeof(float4) * 4 * (size_t)(d.num_bvh_prims - 1);
     }
     d.nodes = nodes;
     d.root_ref = root;
@@ -764,6 +837,9 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "traversal") c->opt_traversal = value;
     else if (k == "strict_fp") c->opt_strict = value;
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
+    else if (k == "large_split") c->opt_large_split = value;          // takes effect at the next commit
+    else if (k == "max_large") c->opt_max_large = value;
+    else if (k == "refill") c->opt_refill = value;  // lanes waiting before a warp leaves the tree to shade
     else if (k == "block_threads") {
         if (value != RTB_BLOCK_THREADS) return fail(c, "rtb_set_option", "block_threads is fixed at build time");
     } else if (k == "blocks_per_sm") c->opt_blocks_per_sm = value;
@@ -803,9 +879,9 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     std::string k(key);
     if (k == "num_prims") *value = c->d.num_prims;
     else if (k == "num_tris") *value = c->d.num_tris;
-    else if (k == "num_quads") *value = c->d.num_quads;
     else if (k == "num_spheres") *value = c->d.num_spheres;
-    else if (k == "num_nodes") *value = c->d.num_prims > 1 ? c->d.num_prims - 1 : 0;
+    else if (k == "num_nodes") *value = c->d.num_bvh_prims > 1 ? c->d.num_bvh_prims - 1 : 0;
+    else if (k == "num_large") *value = c->d.num_large;
     else if (k == "build_ms") *value = c->build_ms;
     else if (k == "scene_bytes") *value = (double)c->scene_bytes;
     else if (k == "culled_tris") *value = c->culled_tris;

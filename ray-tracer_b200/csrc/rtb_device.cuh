@@ -15,8 +15,10 @@ namespace rtb {
 #define RTB_INF_F 1073741824.0f /* INF = 1 << 31 - 1 == 1 << 30, objects.cu:6 */
 #define RTB_EPS 0.000001f      /* FLOAT_PRECISION_ERROR, objects.cu:7 */
 
-// leaf reference kinds (low 2 bits of an encoded leaf id)
-enum { KIND_TRI = 0, KIND_QUAD = 1, KIND_SPHERE = 2 };
+// leaf reference kinds (low 3 bits of an encoded leaf id).  A quad is two consecutive triangles of
+// the same array; the one-way kinds carry OneWayQuad's direction test (objects.cu:273-280).
+enum { KIND_TRI = 0, KIND_QUAD = 1, KIND_SPHERE = 2, KIND_QUAD_ONEWAY = 3, KIND_QUAD_ONEWAY_INV = 4 };
+#define RTB_KIND_BITS 3
 
 // ---- material table entry (64 B): Material + Texture of material.cu:4-186, flattened -----------
 struct DMaterial {
@@ -36,18 +38,22 @@ struct DMaterial {
 // ---- device scene (all pointers device memory, 16-byte aligned) --------------------------------
 struct DScene {
     // LBVH: internal node i = 4 float4: {lo0.xyz, ref0} {hi0.xyz, -} {lo1.xyz, ref1} {hi1.xyz, -}
-    // ref >= 0: internal node index; ref < 0: leaf, ~ref = (index << 2) | kind
+    // ref >= 0: internal node index; ref < 0: leaf, ~ref = (index << 3) | kind
     const float4 *nodes;
-    int num_prims;       // leaves of the LBVH
-    int root_ref;        // encoded like a child ref (a 1-primitive scene has a leaf root)
-    // triangles (KIND_TRI), 3 float4 each: {p0.xyz, s1.x} {s1.yz, s2.xy} {s2.z, n.xyz}
+    int num_prims;       // all primitives (leaves of the LBVH + large primitives)
+    int num_bvh_prims;   // leaves of the LBVH
+    int root_ref;        // encoded like a child ref (a 1-primitive tree has a leaf root)
+    // Large primitives (walls, floors: boxes that span a big share of the scene) are kept out of
+    // the tree and tested first, in a warp-uniform loop; their hits bound the tree traversal.
+    const int *large_refs;
+    const float4 *large_boxes;  // 2 float4 per large primitive: padded lo, hi
+    int num_large;
+    // triangles, 3 float4 each: {p0.xyz, s1.x} {s1.yz, s2.xy} {s2.z, n.xyz}.  KIND_TRI leaves
+    // name one triangle, KIND_QUAD* leaves the first of two consecutive ones (t1, t2 of a Quad).
     const float4 *tris;
     const int2 *tri_ids;     // {object index, sub id}
     const float2 *tri_uv;    // 3 per triangle (Triangle::texture_points)
     const int *tri_refleaf;  // reference-BVH leaf node of a mesh triangle, -1 otherwise
-    // quads (KIND_QUAD): 7 float4 each: tri A (3), tri B (3), {one-way normal.xyz, flags}
-    const float4 *quads;
-    const int2 *quad_ids;    // {object index, sub id of triangle A}
     // spheres (KIND_SPHERE): {center.xyz, radius}
     const float4 *spheres;
     const int *sphere_ids;   // object index
@@ -60,7 +66,7 @@ struct DScene {
     const float4 *ref_nodes;
     // brute-force list (option "traversal" = 1): every leaf ref in creation order
     const int *all_refs;
-    int num_tris, num_quads, num_spheres, num_objects;
+    int num_tris, num_spheres, num_objects;
 };
 
 struct DCamera {  // == DeviceCamData, camera.cu:12-18

@@ -16,6 +16,7 @@ struct RenderParams {
     // screen-tile sharding: this launch renders rows y with (y / band_rows) % world == rank
     int shard_rank, shard_world, band_rows;
     int local_rows;                  // rows owned by this rank
+    int refill;                      // SHADE phase starts when this many lanes of a warp wait (1..32)
     unsigned int *work_counter;      // zeroed before launch
     unsigned long long *counters;    // 6 slots (RtbCounters order) or nullptr
 };

@@ -1,4 +1,4 @@
-// rtb_lbvh.cu -- GPU LBVH build: primitive bounds -> 30-bit Morton codes -> stable LSD radix sort
+// rtb_lbvh.cu -- GPU LBVH build: primitive bounds -> 63-bit Morton codes -> stable LSD radix sort
 // -> Karras (2012) hierarchy -> bottom-up refit -> 64-byte two-child nodes.
 // Replaces the reference's host BVH constructor (src/objects.cu:452-464,602-770: recursive
 // median split by distance to a reference point, fixed depth 10, one cudaMalloc per node) and its
@@ -38,13 +38,13 @@ __device__ __forceinline__ void grow_tri(float3 &lo, float3 &hi, const float4 *T
 __global__ void leaf_bounds_kernel(LbvhInput in, float4 *leaf_lo, float4 *leaf_hi, unsigned int *scene_bounds) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= in.num_prims) return;
-    int enc = ~in.leaf_refs[i], kind = enc & 3, idx = enc >> 2;
+    int enc = ~in.leaf_refs[i], kind = enc & 7, idx = enc >> RTB_KIND_BITS;
     float3 lo = make_float3(3.0e38f, 3.0e38f, 3.0e38f), hi = make_float3(-3.0e38f, -3.0e38f, -3.0e38f);
     if (kind == KIND_TRI) {
         grow_tri(lo, hi, in.tris + 3 * idx);
-    } else if (kind == KIND_QUAD) {
-        grow_tri(lo, hi, in.quads + 7 * idx);
-        grow_tri(lo, hi, in.quads + 7 * idx + 3);
+    } else if (kind != KIND_SPHERE) {
+        grow_tri(lo, hi, in.tris + 3 * idx);
+        grow_tri(lo, hi, in.tris + 3 * idx + 3);
     } else {
         float4 s = in.spheres[idx];
         float r = fabsf(s.w) * 1.000001f;
@@ -58,28 +58,34 @@ __global__ void leaf_bounds_kernel(LbvhInput in, float4 *leaf_lo, float4 *leaf_h
     atomicMax(scene_bounds + 3, enc_float(cx)); atomicMax(scene_bounds + 4, enc_float(cy)); atomicMax(scene_bounds + 5, enc_float(cz));
 }
 
-__device__ __forceinline__ unsigned int expand_bits(unsigned int v) {
-    v = (v * 0x00010001u) & 0xFF0000FFu;
-    v = (v * 0x00000101u) & 0x0F00F00Fu;
-    v = (v * 0x00000011u) & 0xC30C30C3u;
-    v = (v * 0x00000005u) & 0x49249249u;
-    return v;
+// spread the low 21 bits of v so that two zero bits separate consecutive bits
+__device__ __forceinline__ unsigned long long expand_bits21(unsigned int v) {
+    unsigned long long x = v & 0x1fffffull;
+    x = (x | (x << 32)) & 0x1f00000000ffffull;
+    x = (x | (x << 16)) & 0x1f0000ff0000ffull;
+    x = (x | (x << 8)) & 0x100f00f00f00f00full;
+    x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
+    x = (x | (x << 2)) & 0x1249249249249249ull;
+    return x;
 }
 
-// K2: 30-bit Morton code of the leaf centroid
+// K2: 63-bit Morton code of the leaf centroid.  All three axes are quantised with the SAME step
+// (the largest extent / 2^21): cubic cells.  Per-axis normalisation would make the cells of a
+// flat scene (the 40 x 35 instance grid) needle-thin along the short axis and the tree poor.
 __global__ void morton_kernel(int n, const float4 *leaf_lo, const float4 *leaf_hi, const unsigned int *scene_bounds,
-                              unsigned int *keys, int *vals) {
+                              unsigned long long *keys, int *vals) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float3 mn = make_float3(dec_float(scene_bounds[0]), dec_float(scene_bounds[1]), dec_float(scene_bounds[2]));
     float3 mx = make_float3(dec_float(scene_bounds[3]), dec_float(scene_bounds[4]), dec_float(scene_bounds[5]));
     float4 lo = leaf_lo[i], hi = leaf_hi[i];
-    float ex = fmaxf(mx.x - mn.x, 1e-30f), ey = fmaxf(mx.y - mn.y, 1e-30f), ez = fmaxf(mx.z - mn.z, 1e-30f);
-    float x = (0.5f * (lo.x + hi.x) - mn.x) / ex, y = (0.5f * (lo.y + hi.y) - mn.y) / ey, z = (0.5f * (lo.z + hi.z) - mn.z) / ez;
-    unsigned int xi = (unsigned int)fminf(fmaxf(x * 1024.f, 0.f), 1023.f);
-    unsigned int yi = (unsigned int)fminf(fmaxf(y * 1024.f, 0.f), 1023.f);
-    unsigned int zi = (unsigned int)fminf(fmaxf(z * 1024.f, 0.f), 1023.f);
-    keys[i] = (expand_bits(xi) << 2) | (expand_bits(yi) << 1) | expand_bits(zi);
+    float extent = fmaxf(fmaxf(mx.x - mn.x, mx.y - mn.y), fmaxf(mx.z - mn.z, 1e-30f));
+    float scale = 2097152.f / extent;
+    float x = (0.5f * (lo.x + hi.x) - mn.x) * scale, y = (0.5f * (lo.y + hi.y) - mn.y) * scale, z = (0.5f * (lo.z + hi.z) - mn.z) * scale;
+    unsigned int xi = (unsigned int)fminf(fmaxf(x, 0.f), 2097151.f);
+    unsigned int yi = (unsigned int)fminf(fmaxf(y, 0.f), 2097151.f);
+    unsigned int zi = (unsigned int)fminf(fmaxf(z, 0.f), 2097151.f);
+    keys[i] = (expand_bits21(xi) << 2) | (expand_bits21(yi) << 1) | expand_bits21(zi);
     vals[i] = i;
 }
 
@@ -88,14 +94,14 @@ constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 8;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 
-__global__ void sort_hist_kernel(int n, const unsigned int *keys, int shift, unsigned int *block_hist, int num_blocks) {
+__global__ void sort_hist_kernel(int n, const unsigned long long *keys, int shift, unsigned int *block_hist, int num_blocks) {
     __shared__ unsigned int hist[256];
     hist[threadIdx.x] = 0;
     __syncthreads();
     int base = blockIdx.x * SORT_TILE;
     for (int k = 0; k < SORT_ITEMS; k++) {
         int i = base + k * SORT_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&hist[(keys[i] >> shift) & 255u], 1u);
+        if (i < n) atomicAdd(&hist[(unsigned int)(keys[i] >> shift) & 255u], 1u);
     }
     __syncthreads();
     block_hist[threadIdx.x * num_blocks + blockIdx.x] = hist[threadIdx.x];  // digit-major
@@ -134,7 +140,7 @@ __global__ void sort_scan_kernel(unsigned int *data, int n) {
     }
 }
 
-__global__ void sort_scatter_kernel(int n, const unsigned int *keys_in, const int *vals_in, unsigned int *keys_out, int *vals_out,
+__global__ void sort_scatter_kernel(int n, const unsigned long long *keys_in, const int *vals_in, unsigned long long *keys_out, int *vals_out,
                                     int shift, const unsigned int *block_offsets, int num_blocks) {
     __shared__ unsigned int next_pos[256];  // next output slot of this block for each digit
     next_pos[threadIdx.x] = block_offsets[threadIdx.x * num_blocks + blockIdx.x];
@@ -144,8 +150,8 @@ __global__ void sort_scatter_kernel(int n, const unsigned int *keys_in, const in
     for (int k = 0; k < SORT_ITEMS; k++) {
         int i = base + k * SORT_THREADS + threadIdx.x;
         bool valid = i < n;
-        unsigned int key = valid ? keys_in[i] : 0xffffffffu;
-        unsigned int digit = (key >> shift) & 255u;
+        unsigned long long key = valid ? keys_in[i] : ~0ull;
+        unsigned int digit = (unsigned int)(key >> shift) & 255u;
         // stable rank: warps take their turn in order, lanes in order inside a warp
         unsigned int peers = __match_any_sync(0xffffffffu, valid ? digit : 256u);
         unsigned int rank = __popc(peers & ((1u << lane) - 1u));
@@ -171,15 +177,15 @@ __global__ void sort_scatter_kernel(int n, const unsigned int *keys_in, const in
 }
 
 // ---- Karras 2012 ---------------------------------------------------------------------------------
-__device__ __forceinline__ int delta(const unsigned int *keys, int n, int i, int j) {
+__device__ __forceinline__ int delta(const unsigned long long *keys, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
-    unsigned int a = keys[i], b = keys[j];
-    if (a != b) return __clz(a ^ b);
-    return 32 + __clz((unsigned int)i ^ (unsigned int)j);  // duplicate codes: fall back to the position
+    unsigned long long a = keys[i], b = keys[j];
+    if (a != b) return __clzll(a ^ b);
+    return 64 + __clz((unsigned int)i ^ (unsigned int)j);  // duplicate codes: fall back to the position
 }
 
 // child encoding during the build: >= 0 internal node, < 0 leaf ~sorted_position
-__global__ void karras_kernel(int n, const unsigned int *keys, int2 *children, int *parent_internal, int *parent_leaf) {
+__global__ void karras_kernel(int n, const unsigned long long *keys, int2 *children, int *parent_internal, int *parent_leaf) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
@@ -275,7 +281,8 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
     const int T = 256, B = (n + T - 1) / T;
     const int sort_blocks = (n + SORT_TILE - 1) / SORT_TILE;
     float4 *leaf_lo = nullptr, *leaf_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr, *nodes = nullptr;
-    unsigned int *keys = nullptr, *keys2 = nullptr, *hist = nullptr, *bounds = nullptr;
+    unsigned long long *keys = nullptr, *keys2 = nullptr;
+    unsigned int *hist = nullptr, *bounds = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *parent_internal = nullptr, *parent_leaf = nullptr, *flags = nullptr;
     int2 *children = nullptr;
     LBVH_CHECK(cudaMalloc(&leaf_lo, sizeof(float4) * n));
@@ -283,8 +290,8 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
     LBVH_CHECK(cudaMalloc(&node_lo, sizeof(float4) * n));
     LBVH_CHECK(cudaMalloc(&node_hi, sizeof(float4) * n));
     LBVH_CHECK(cudaMalloc(&nodes, sizeof(float4) * 4 * (size_t)(n - 1)));
-    LBVH_CHECK(cudaMalloc(&keys, sizeof(unsigned int) * n));
-    LBVH_CHECK(cudaMalloc(&keys2, sizeof(unsigned int) * n));
+    LBVH_CHECK(cudaMalloc(&keys, sizeof(unsigned long long) * n));
+    LBVH_CHECK(cudaMalloc(&keys2, sizeof(unsigned long long) * n));
     LBVH_CHECK(cudaMalloc(&vals, sizeof(int) * n));
     LBVH_CHECK(cudaMalloc(&vals2, sizeof(int) * n));
     LBVH_CHECK(cudaMalloc(&hist, sizeof(unsigned int) * 256 * (size_t)sort_blocks));
@@ -298,11 +305,11 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
     init_bounds_kernel<<<1, 32, 0, st>>>(bounds);
     leaf_bounds_kernel<<<B, T, 0, st>>>(in, leaf_lo, leaf_hi, bounds);
     morton_kernel<<<B, T, 0, st>>>(n, leaf_lo, leaf_hi, bounds, keys, vals);
-    for (int shift = 0; shift < 32; shift += 8) {
+    for (int shift = 0; shift < 64; shift += 8) {
         sort_hist_kernel<<<sort_blocks, SORT_THREADS, 0, st>>>(n, keys, shift, hist, sort_blocks);
         sort_scan_kernel<<<1, 1024, 0, st>>>(hist, 256 * sort_blocks);
         sort_scatter_kernel<<<sort_blocks, SORT_THREADS, 0, st>>>(n, keys, vals, keys2, vals2, shift, hist, sort_blocks);
-        unsigned int *tk = keys; keys = keys2; keys2 = tk;
+        unsigned long long *tk = keys; keys = keys2; keys2 = tk;
         int *tv = vals; vals = vals2; vals2 = tv;
     }
     karras_kernel<<<B, T, 0, st>>>(n, keys, children, parent_internal, parent_leaf);

@@ -6,9 +6,8 @@ namespace rtb {
 
 struct LbvhInput {
     int num_prims;
-    const int *leaf_refs;    // device: encoded leaf refs (~((index << 2) | kind)), creation order
+    const int *leaf_refs;    // device: encoded leaf refs (~((index << 3) | kind)), creation order
     const float4 *tris;      // device primitive records (layout in rtb_device.cuh)
-    const float4 *quads;
     const float4 *spheres;
 };
 

@@ -20,11 +20,11 @@ struct Surface {
 
 // RayHitData of the winning primitive (objects.cu:55-68,154-160) + the object's material index
 __device__ __forceinline__ void make_surface(const DScene &s, const Ray &r, const Best &b, Surface &sf) {
-    int kind = b.code & 3, idx = b.code >> 3;
+    int idx = b.code >> 1;
     sf.point = r.d * b.t + r.o;  // Ray::get_pos, ray.cu:63-65
     sf.u = 0; sf.v = 0;
     int obj;
-    if (kind == KIND_SPHERE) {
+    if (b.code & 1) {
         float4 sp = __ldg(s.spheres + idx);
         V3 c = v3(sp.x, sp.y, sp.z);
         sf.normal = normalised(sf.point - c);
@@ -42,14 +42,8 @@ __device__ __forceinline__ void make_surface(const DScene &s, const Ray &r, cons
         }
         return;
     }
-    const float4 *T;
-    if (kind == KIND_TRI) {
-        T = s.tris + 3 * idx;
-        obj = __ldg(s.tri_ids + idx).x;
-    } else {
-        T = s.quads + 7 * idx + 3 * ((b.code >> 2) & 1);
-        obj = __ldg(s.quad_ids + idx).x;
-    }
+    const float4 *T = s.tris + 3 * idx;
+    obj = __ldg(s.tri_ids + idx).x;
     float4 c = __ldg(T + 2);
     V3 n = v3(c.y, c.z, c.w);
     sf.normal = n * (float)(1 - 2 * (dot(n, r.d) > 0));  // objects.cu:158
@@ -57,14 +51,7 @@ __device__ __forceinline__ void make_surface(const DScene &s, const Ray &r, cons
     if (__ldg(&s.materials[sf.material].need_uv)) {
         // assign_texture_coords(hit, w, u, v): tp0*w + tp1*u + tp2*v, objects.cu:160,196-199
         float w = 1 - b.u - b.v;
-        float2 t0, t1, t2;
-        if (kind == KIND_TRI) {
-            t0 = __ldg(s.tri_uv + 3 * idx); t1 = __ldg(s.tri_uv + 3 * idx + 1); t2 = __ldg(s.tri_uv + 3 * idx + 2);
-        } else if ((b.code >> 2) & 1) {  // Quad::create_triangles, objects.cu:246-252
-            t0 = make_float2(0, 0); t1 = make_float2(0, 1); t2 = make_float2(1, 1);
-        } else {
-            t0 = make_float2(0, 0); t1 = make_float2(1, 0); t2 = make_float2(1, 1);
-        }
+        float2 t0 = __ldg(s.tri_uv + 3 * idx), t1 = __ldg(s.tri_uv + 3 * idx + 1), t2 = __ldg(s.tri_uv + 3 * idx + 2);
         sf.u = (t0.x * w + t1.x * b.u) + t2.x * b.v;
         sf.v = (t0.y * w + t1.y * b.u) + t2.y * b.v;
     }
@@ -175,12 +162,21 @@ __device__ __forceinline__ int shard_row(const RenderParams &p, int local_row) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Persistent megakernel.  One lane owns one pixel at a time and runs the reference's per-pixel
-// function (get_pixel_colour -> get_ray_colour -> trace_ray, raytracer.cu:67-136) as a state
-// machine whose unit of work is ONE SEGMENT, so that all 32 lanes of a warp are inside the
-// traversal together no matter which sample / bounce each is at.  The samples of a pixel stay
-// serial in their lane because the RNG state is per pixel and carried from sample to sample
-// (SURVEY.md F10/H1).  Pixels are handed out in 8x4 tiles through one atomic counter.
+// Persistent megakernel with dynamic fetch.
+//
+// One lane owns one pixel at a time and runs the reference's per-pixel function (get_pixel_colour
+// -> get_ray_colour -> trace_ray, raytracer.cu:67-136).  The samples of a pixel stay serial in
+// their lane because the RNG state is per pixel and carried from sample to sample (SURVEY.md
+// F10/H1).  Pixels are handed out in 8x4 tiles through one atomic counter.
+//
+// The warp alternates between two phases so that neither runs with mostly idle lanes:
+//   SHADE    lanes whose ray has finished shade the hit, advance their sample / bounce / pixel
+//            state machine, generate the next ray (antialias jitter) and test it against the large
+//            primitives;
+//   TRAVERSE lanes with a live ray walk the LBVH (resumable state in `Trav`).
+// A lane that finishes its ray early waits only until `p.refill` lanes of the warp are waiting
+// (or nobody traverses any more); then the SHADE phase runs for all of them at once while the long
+// rays keep their traversal state, and everybody re-enters TRAVERSE together.
 // ---------------------------------------------------------------------------------------------
 template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_megakernel(const RenderParams p) {
@@ -191,13 +187,17 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     const V3 cam_o = v3(p.cam.cam_pos[0], p.cam.cam_pos[1], p.cam.cam_pos[2]);
     const int tiles_x = (p.width + 7) >> 3, tiles_y = (p.local_rows + 3) >> 2;
     const unsigned int total = (unsigned int)tiles_x * tiles_y * 32u;
+    const unsigned int FULL = 0xffffffffu;
+    const int refill = p.refill, min_active = 32 - p.refill + 1;
 
     Counters cnt;
-    unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
-#ifdef RTB_COUNTERS
     cnt.box = cnt.tri = cnt.sph = 0;
-#endif
+    unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
 
+    // lane state
+    enum { IDLE = 0, WAITING = 1, TRAVERSING = 2 };
+    int mode = WAITING;    // WAITING: needs the SHADE phase; IDLE: out of work
+    bool pending = false;  // a finished ray whose hit has not been shaded yet
     int array_index = -1;  // (y * W + x) * 3 of the pixel this lane owns, -1 = none
     uint32_t rng = 0;
     int sample = 0, bounce = 0;
@@ -206,81 +206,111 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     ray.o = cam_o; ray.d = pdir; ray.inv = pdir;
     V3 thr = v3(1, 1, 1), col = v3(0, 0, 0), acc = v3(0, 0, 0);
     float cur_n = 1;
+    Trav T;
+    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0;
+    T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
 
     for (;;) {
-        if (array_index < 0) {
-            unsigned int idx = atomicAdd(p.work_counter, 1u);
-            if (idx >= total) break;
-            unsigned int tile = idx >> 5, within = idx & 31u;
-            int x = (int)(tile % tiles_x) * 8 + (int)(within & 7u);
-            int ly = (int)(tile / tiles_x) * 4 + (int)(within >> 3);
-            if (x >= p.width || ly >= p.local_rows) continue;
-            int y = shard_row(p, ly);
-            if (y >= p.height) continue;
-            array_index = (y * p.width + x) * 3;  // raytracer.cu:123
-            rng = rng_seed(array_index, p.time_ms);
-            pdir = primary_direction(p.cam, x, y);
-            acc = v3(0, 0, 0);
-            sample = 0;
-            bounce = 0;
-        }
-        if (bounce == 0) {
-            if (sample >= spp) {
-                // get_ray_colour, raytracer.cu:107-112
-                V3 colour = acc / (float)spp;
-                V3 previous = v3(p.prev[array_index], p.prev[array_index + 1], p.prev[array_index + 2]);
-                V3 previous_sum = previous * (float)p.frame_num;
-                V3 res = (colour + previous_sum) / (float)(p.frame_num + 1);
-                p.out[array_index] = res.x;
-                p.out[array_index + 1] = res.y;
-                p.out[array_index + 2] = res.z;
-                array_index = -1;
-                continue;
+        unsigned int waiting = __ballot_sync(FULL, mode == WAITING);
+        unsigned int traversing = __ballot_sync(FULL, mode == TRAVERSING);
+        if (!waiting && !traversing) break;  // every lane is out of work
+        if (waiting && (!traversing || __popc(waiting) >= refill)) {
+            // ------------------------------- SHADE phase -------------------------------------
+            if (mode == WAITING) {
+                if (pending) {  // raytracer.cu:74-91 for the ray that just finished
+                    pending = false;
+                    if (COUNT) n_seg++;
+                    bool end_sample;
+                    if (T.best.code < 0) {
+                        col = col + sky * thr;
+                        end_sample = true;
+                    } else {
+                        if (COUNT) n_hit++;
+                        Surface sf;
+                        make_surface(s, ray, T.best, sf);
+                        const DMaterial &m = s.materials[sf.material];
+                        int mtype = __ldg(&m.type);
+                        if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), cur_n, rng);
+                        else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), rng);
+                        if (mtype == 1) col = col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * thr;
+                        else thr = thr * texture_colour(s, m, sf.u, sf.v);
+                        bounce++;
+                        end_sample = bounce >= limit;
+                    }
+                    if (end_sample) {
+                        acc = acc + col;
+                        sample++;
+                        bounce = 0;
+                    }
+                }
+                // advance the state machine until this lane holds a ray to trace (or runs dry)
+                for (;;) {
+                    if (array_index < 0) {
+                        unsigned int idx = atomicAdd(p.work_counter, 1u);
+                        if (idx >= total) { mode = IDLE; break; }
+                        unsigned int tile = idx >> 5, within = idx & 31u;
+                        int x = (int)(tile % tiles_x) * 8 + (int)(within & 7u);
+                        int ly = (int)(tile / tiles_x) * 4 + (int)(within >> 3);
+                        if (x >= p.width || ly >= p.local_rows) continue;
+                        int y = shard_row(p, ly);
+                        if (y >= p.height) continue;
+                        array_index = (y * p.width + x) * 3;  // raytracer.cu:123
+                        rng = rng_seed(array_index, p.time_ms);
+                        pdir = primary_direction(p.cam, x, y);
+                        acc = v3(0, 0, 0);
+                        sample = 0;
+                        bounce = 0;
+                    }
+                    if (bounce == 0) {
+                        if (sample >= spp) {  // get_ray_colour, raytracer.cu:107-112
+                            V3 colour = acc / (float)spp;
+                            V3 previous = v3(p.prev[array_index], p.prev[array_index + 1], p.prev[array_index + 2]);
+                            V3 previous_sum = previous * (float)p.frame_num;
+                            V3 res = (colour + previous_sum) / (float)(p.frame_num + 1);
+                            p.out[array_index] = res.x;
+                            p.out[array_index + 1] = res.y;
+                            p.out[array_index + 2] = res.z;
+                            array_index = -1;
+                            continue;
+                        }
+                        // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
+                        ray.o = cam_o;
+                        change_direction(ray, pdir);
+                        cur_n = 1;
+                        thr = v3(1, 1, 1);
+                        col = v3(0, 0, 0);
+                        if (COUNT) n_samples++;
+                        if (limit <= 0) { sample++; continue; }
+                    }
+                    break;  // a ray is ready
+                }
+                if (mode != IDLE) {
+                    if (aa) apply_antialias(ray, rng);
+                    if (BRUTE) {
+                        T.best = trace_brute(s, ray, cnt);
+                        T.cur = RTB_DONE; T.leaf = 0;
+                    } else {
+                        trav_begin(s, ray, T, cnt);
+                    }
+                    mode = TRAVERSING;
+                }
             }
-            // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
-            ray.o = cam_o;
-            change_direction(ray, pdir);
-            cur_n = 1;
-            thr = v3(1, 1, 1);
-            col = v3(0, 0, 0);
-            if (COUNT) n_samples++;
-            if (limit <= 0) { sample++; continue; }
         }
-        // ---- one segment: raytracer.cu:70-91 ----
-        if (aa) apply_antialias(ray, rng);
-        Best best = trace<BRUTE>(s, ray, cnt);
-        if (COUNT) n_seg++;
-        bool end_sample;
-        if (best.code < 0) {
-            col = col + sky * thr;
-            end_sample = true;
-        } else {
-            if (COUNT) n_hit++;
-            Surface sf;
-            make_surface(s, ray, best, sf);
-            const DMaterial &m = s.materials[sf.material];
-            int mtype = __ldg(&m.type);
-            if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), cur_n, rng);
-            else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), rng);
-            if (mtype == 1) col = col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * thr;
-            else thr = thr * texture_colour(s, m, sf.u, sf.v);
-            bounce++;
-            end_sample = bounce >= limit;
-        }
-        if (end_sample) {
-            acc = acc + col;
-            sample++;
-            bounce = 0;
+        // --------------------------------- TRAVERSE phase --------------------------------------
+        if (mode == TRAVERSING) {
+            if (!BRUTE) trav_run(s, ray, T, min_active, cnt);
+            if (trav_done(T)) {
+                mode = WAITING;
+                pending = true;
+            }
         }
     }
     if (COUNT && p.counters) {
         atomicAdd(p.counters + 0, n_seg);
         atomicAdd(p.counters + 1, n_hit);
-#ifdef RTB_COUNTERS
         atomicAdd(p.counters + 2, cnt.box);
         atomicAdd(p.counters + 3, cnt.tri);
         atomicAdd(p.counters + 4, cnt.sph);
-#endif
         atomicAdd(p.counters + 5, n_samples);
     }
 }

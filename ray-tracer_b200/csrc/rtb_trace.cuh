@@ -10,7 +10,7 @@ struct Ray {
     V3 o, d, inv;  // origin, direction (normalised), 1/direction (ray.cu:198-202)
 };
 
-// best candidate so far.  code = (index << 3) | (which << 2) | kind, or -1 for none.
+// best candidate so far.  code = (index << 1) | is_sphere with index into tris / spheres, -1 = none.
 struct Best {
     float t, u, v;  // distance and the barycentrics Triangle::hit computes (objects.cu:143-146)
     int code;
@@ -60,14 +60,8 @@ __device__ __forceinline__ bool sphere_test(float4 s, const Ray &r, float &t) {
 
 // ---- ids and the tie rule --------------------------------------------------------------------
 __device__ __forceinline__ int2 code_ids(const DScene &s, int code) {
-    int kind = code & 3, idx = code >> 3;
-    if (kind == KIND_TRI) return __ldg(s.tri_ids + idx);
-    if (kind == KIND_QUAD) {
-        int2 q = __ldg(s.quad_ids + idx);
-        q.y += (code >> 2) & 1;
-        return q;
-    }
-    return make_int2(__ldg(s.sphere_ids + idx), 0);
+    if (code & 1) return make_int2(__ldg(s.sphere_ids + (code >> 1)), 0);
+    return __ldg(s.tri_ids + (code >> 1));
 }
 
 // Exact tie (bit-equal t).  Across objects the reference keeps the LATER object (`<=`,
@@ -103,35 +97,34 @@ __device__ __forceinline__ void consider(const DScene &s, Best &best, float t, f
     }
 }
 
-// test one leaf (ref < 0) and fold it into `best`
+// test one leaf (ref < 0) and fold it into `best`.  One code path serves single triangles and
+// quads (two consecutive triangles) so that lanes holding either kind stay converged.
 __device__ __forceinline__ void test_leaf(const DScene &s, const Ray &r, int ref, Best &best, Counters &cnt) {
-    int enc = ~ref, kind = enc & 3, idx = enc >> 2;
+    int enc = ~ref, kind = enc & 7, idx = enc >> RTB_KIND_BITS;
     float t, u = 0, v = 0;
-    if (kind == KIND_TRI) {
+    if (kind == KIND_SPHERE) {
+        RTB_COUNT(cnt, sph);
+        if (sphere_test(__ldg(s.spheres + idx), r, t)) consider(s, best, t, 0.f, 0.f, (idx << 1) | 1);
+        return;
+    }
+    if (kind >= KIND_QUAD_ONEWAY) {
+        // OneWayQuad::hit, objects.cu:273-280; normal_vec = t1.normal * (1 - 2*invert), :285-289
+        float4 c = __ldg(s.tris + 3 * idx + 2);
+        float m = (float)(1 - 2 * (kind == KIND_QUAD_ONEWAY_INV));
+        if (dot(r.d, v3(c.y * m, c.z * m, c.w * m)) < 0) return;
+    }
+    // Quad::hit, objects.cu:223-236: triangle 1 if it hits, else whatever triangle 2 says
+    int count = kind == KIND_TRI ? 1 : 2;
+    for (int k = 0; k < count; k++) {
         RTB_COUNT(cnt, tri);
-        if (tri_test(s.tris + 3 * idx, r, t, u, v)) {
-            if (r.d.x == 0 || r.d.y == 0 || r.d.z == 0) {
+        if (tri_test(s.tris + 3 * (idx + k), r, t, u, v)) {
+            if (kind == KIND_TRI && (r.d.x == 0 || r.d.y == 0 || r.d.z == 0)) {
                 int leaf = __ldg(s.tri_refleaf + idx);
                 if (leaf >= 0 && !ref_path_hit(s, leaf, r)) return;
             }
-            consider(s, best, t, u, v, (idx << 3) | KIND_TRI);
+            consider(s, best, t, u, v, (idx + k) << 1);
+            return;
         }
-    } else if (kind == KIND_QUAD) {
-        const float4 *Q = s.quads + 7 * idx;
-        float4 ow = __ldg(Q + 6);
-        // OneWayQuad::hit, objects.cu:273-280
-        if (__float_as_int(ow.w) != 0 && dot(r.d, v3(ow.x, ow.y, ow.z)) < 0) return;
-        // Quad::hit, objects.cu:223-236: triangle 1 if it hits, else whatever triangle 2 says
-        RTB_COUNT(cnt, tri);
-        if (tri_test(Q, r, t, u, v)) {
-            consider(s, best, t, u, v, (idx << 3) | KIND_QUAD);
-        } else {
-            RTB_COUNT(cnt, tri);
-            if (tri_test(Q + 3, r, t, u, v)) consider(s, best, t, u, v, (idx << 3) | 4 | KIND_QUAD);
-        }
-    } else {
-        RTB_COUNT(cnt, sph);
-        if (sphere_test(__ldg(s.spheres + idx), r, t)) consider(s, best, t, 0.f, 0.f, (idx << 3) | KIND_SPHERE);
     }
 }
 
@@ -153,19 +146,48 @@ __device__ __forceinline__ bool box_test(float4 lo, float4 hi, const Ray &r, flo
 }
 
 #ifndef RTB_STACK
-#define RTB_STACK 64
+#define RTB_STACK 96
 #endif
 
-// closest hit over the whole scene through the LBVH
-__device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, Counters &cnt) {
+#define RTB_DONE 0x7fffffff
+
+// Resumable traversal state of one ray: lives in the lane across iterations of the megakernel's
+// scheduling loop, so that lanes whose rays end early can go and shade / fetch new rays while the
+// long rays of the warp keep their place in the tree (dynamic fetch, Aila & Laine 2009).
+struct Trav {
     Best best;
-    best.t = RTB_INF_F; best.u = 0; best.v = 0; best.code = -1;
-    if (s.num_prims == 0) return best;
+    int cur;   // >= 0 internal node, < 0 leaf, RTB_DONE finished
+    int leaf;  // postponed leaf (< 0) or 0
+    int sp;
     int stack[RTB_STACK];
-    int sp = 0;
-    int cur = s.root_ref;
-    for (;;) {
-        if (cur >= 0) {
+};
+
+__device__ __forceinline__ bool trav_done(const Trav &T) { return T.cur == RTB_DONE && T.leaf == 0; }
+
+// start a ray: large primitives first (same address in every lane: converged, broadcast loads;
+// the hit they give culls most of the tree), then point the cursor at the root
+__device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, Counters &cnt) {
+    T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
+    for (int i = 0; i < s.num_large; i++) {
+        float tn;
+        RTB_COUNT(cnt, box);
+        if (box_test(__ldg(s.large_boxes + 2 * i), __ldg(s.large_boxes + 2 * i + 1), r, T.best.t * 1.0001f, tn))
+            test_leaf(s, r, __ldg(s.large_refs + i), T.best, cnt);
+    }
+    T.sp = 0;
+    T.leaf = 0;
+    T.cur = s.num_bvh_prims > 0 ? s.root_ref : RTB_DONE;
+}
+
+// Advance the ray through the LBVH: "while-while" traversal with postponed leaves -- every lane
+// walks internal nodes until it holds a leaf, then the warp tests leaves together, so the (long)
+// primitive test is issued for many lanes at once.  Returns when the ray is finished or when fewer
+// than `min_active` lanes of the warp are still traversing (0 = run to completion).
+__device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, int min_active, Counters &cnt) {
+    int cur = T.cur, leaf = T.leaf, sp = T.sp;
+    Best best = T.best;
+    while (cur != RTB_DONE || leaf < 0) {
+        while (cur >= 0 && cur != RTB_DONE) {
             const float4 *N = s.nodes + 4 * cur;
             float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
             // relative slack on the distance cull: a primitive's own t carries more rounding than
@@ -179,19 +201,40 @@ __device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, Counter
             int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
             if (h0 && h1) {
                 bool first0 = n0 <= n1;
-                if (sp < RTB_STACK) stack[sp++] = first0 ? r1 : r0;
                 cur = first0 ? r0 : r1;
-                continue;
+                if (sp < RTB_STACK) T.stack[sp++] = first0 ? r1 : r0;
+            } else if (h0) {
+                cur = r0;
+            } else if (h1) {
+                cur = r1;
+            } else {
+                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
             }
-            if (h0) { cur = r0; continue; }
-            if (h1) { cur = r1; continue; }
-        } else {
-            test_leaf(s, r, cur, best, cnt);
+            if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
+                leaf = cur;
+                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+            }
+            if (!__any_sync(__activemask(), leaf == 0)) break;  // every lane here holds a leaf
         }
-        if (sp == 0) break;
-        cur = stack[--sp];
+        while (leaf < 0) {
+            test_leaf(s, r, leaf, best, cnt);
+            leaf = 0;
+            if (cur < 0) {  // a second leaf was reached while the first was pending
+                leaf = cur;
+                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+            }
+        }
+        if (__popc(__activemask()) < min_active) break;  // too few lanes left: let the others refill
     }
-    return best;
+    T.cur = cur; T.leaf = leaf; T.sp = sp; T.best = best;
+}
+
+// closest hit over the whole scene through the LBVH, in one go
+__device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, Counters &cnt) {
+    Trav T;
+    trav_begin(s, r, T, cnt);
+    trav_run(s, r, T, 0, cnt);
+    return T.best;
 }
 
 // brute force over every primitive in creation order (option "traversal" = 1): the LBVH's checker
