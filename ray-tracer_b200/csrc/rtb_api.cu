@@ -59,7 +59,7 @@ struct rtb_ctx {
     bool timing_pending = false;
 
     // options
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 12;
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_node_exit = 4;
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
 };
@@ -354,6 +354,7 @@ int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
     p.refill = c->opt_refill < 1 ? 1 : (c->opt_refill > 32 ? 32 : c->opt_refill);
+    p.node_exit = c->opt_node_exit < 0 ? 0 : (c->opt_node_exit > 31 ? 31 : c->opt_node_exit);
     p.work_counter = c->d_work;
     p.counters = c->opt_counters ? c->d_counters : nullptr;
     RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
@@ -840,6 +841,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "large_split") c->opt_large_split = value;          // takes effect at the next commit
     else if (k == "max_large") c->opt_max_large = value;
     else if (k == "refill") c->opt_refill = value;  // lanes waiting before a warp leaves the tree to shade
+    else if (k == "node_exit") c->opt_node_exit = value;
     else if (k == "block_threads") {
         if (value != RTB_BLOCK_THREADS) return fail(c, "rtb_set_option", "block_threads is fixed at build time");
     } else if (k == "blocks_per_sm") c->opt_blocks_per_sm = value;

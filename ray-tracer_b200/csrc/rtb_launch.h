@@ -17,6 +17,7 @@ struct RenderParams {
     int shard_rank, shard_world, band_rows;
     int local_rows;                  // rows owned by this rank
     int refill;                      // SHADE phase starts when this many lanes of a warp wait (1..32)
+    int node_exit;                   // NODE phase ends when at most this many lanes still look for a first leaf
     unsigned int *work_counter;      // zeroed before launch
     unsigned long long *counters;    // 6 slots (RtbCounters order) or nullptr
 };

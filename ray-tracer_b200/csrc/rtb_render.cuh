@@ -149,9 +149,9 @@ __device__ __forceinline__ V3 primary_direction(const DCamera &c, int x, int y) 
     return normalised(view_pos - o);
 }
 
-template <bool BRUTE> __device__ __forceinline__ Best trace(const DScene &s, const Ray &r, Counters &cnt) {
+template <bool BRUTE> __device__ __forceinline__ Best trace(const DScene &s, const Ray &r, unsigned mask, Counters &cnt) {
     if (BRUTE) return trace_brute(s, r, cnt);
-    return trace_bvh(s, r, cnt);
+    return trace_bvh(s, r, mask, cnt);
 }
 
 // local row index -> global row for the row-cyclic band sharding (SURVEY.md 8(e) partitioning A)
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     const int tiles_x = (p.width + 7) >> 3, tiles_y = (p.local_rows + 3) >> 2;
     const unsigned int total = (unsigned int)tiles_x * tiles_y * 32u;
     const unsigned int FULL = 0xffffffffu;
-    const int refill = p.refill, min_active = 32 - p.refill + 1;
+    const int refill = p.refill, node_exit = p.node_exit;
 
     Counters cnt;
     cnt.box = cnt.tri = cnt.sph = 0;
@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     enum { IDLE = 0, WAITING = 1, TRAVERSING = 2 };
     int mode = WAITING;    // WAITING: needs the SHADE phase; IDLE: out of work
     bool pending = false;  // a finished ray whose hit has not been shaded yet
+    bool fresh = false;    // a new ray that has not entered the tree yet
     int array_index = -1;  // (y * W + x) * 3 of the pixel this lane owns, -1 = none
     uint32_t rng = 0;
     int sample = 0, bounce = 0;
@@ -286,19 +287,28 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
                 }
                 if (mode != IDLE) {
                     if (aa) apply_antialias(ray, rng);
-                    if (BRUTE) {
-                        T.best = trace_brute(s, ray, cnt);
-                        T.cur = RTB_DONE; T.leaf = 0;
-                    } else {
-                        trav_begin(s, ray, T, cnt);
-                    }
+                    fresh = true;
                     mode = TRAVERSING;
+                }
+            }
+            // new rays start together: large primitives, then the cursor goes to the root
+            unsigned starting = __ballot_sync(FULL, fresh);
+            if (fresh) {
+                fresh = false;
+                if (BRUTE) {
+                    T.best = trace_brute(s, ray, cnt);
+                    T.cur = RTB_DONE; T.leaf = 0;
+                } else {
+                    trav_begin(s, ray, T, starting, cnt);
                 }
             }
         }
         // --------------------------------- TRAVERSE phase --------------------------------------
+        unsigned tmask = __ballot_sync(FULL, mode == TRAVERSING);
+        // leave the tree once `refill` lanes of the warp wait for the SHADE phase
+        int quota = refill - __popc(__ballot_sync(FULL, mode == WAITING));
         if (mode == TRAVERSING) {
-            if (!BRUTE) trav_run(s, ray, T, min_active, cnt);
+            if (!BRUTE) trav_run(s, ray, T, tmask, quota < 1 ? 1 : quota, node_exit, cnt);
             if (trav_done(T)) {
                 mode = WAITING;
                 pending = true;
@@ -318,7 +328,9 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
 // primary-hit ids, antialias off; one thread per pixel
 template <bool BRUTE> __global__ void primary_ids_kernel(const IdsParams p) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
-    if (x >= p.width || y >= p.height) return;
+    // out-of-frame lanes trace too (the traversal is warp-synchronous) and write nothing
+    const bool valid = x < p.width && y < p.height;
+    const unsigned mask = 0xffffffffu;
     Ray ray;
     ray.o = v3(p.cam.cam_pos[0], p.cam.cam_pos[1], p.cam.cam_pos[2]);
     change_direction(ray, primary_direction(p.cam, x, y));
@@ -326,8 +338,9 @@ template <bool BRUTE> __global__ void primary_ids_kernel(const IdsParams p) {
 #ifdef RTB_COUNTERS
     cnt.box = cnt.tri = cnt.sph = 0;
 #endif
-    Best best = trace<BRUTE>(p.scene, ray, cnt);
+    Best best = trace<BRUTE>(p.scene, ray, mask, cnt);
     size_t i = (size_t)y * p.width + x;
+    if (!valid) return;
     if (best.code < 0) {
         p.obj_id[i] = -1; p.sub_id[i] = -1; p.t[i] = RTB_INF_F;
     } else {

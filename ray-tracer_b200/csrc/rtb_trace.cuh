@@ -164,59 +164,84 @@ struct Trav {
 
 __device__ __forceinline__ bool trav_done(const Trav &T) { return T.cur == RTB_DONE && T.leaf == 0; }
 
-// start a ray: large primitives first (same address in every lane: converged, broadcast loads;
-// the hit they give culls most of the tree), then point the cursor at the root
-__device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, Counters &cnt) {
+// start a ray: large primitives first (the hit they give culls most of the tree), then point the
+// cursor at the root.  `mask` = the lanes of the warp that call this together.  The box tests run
+// converged (same address in every lane: broadcast loads) and only record which large primitives
+// the ray may touch; the primitive tests then run in a warp-synchronous loop in which every lane
+// pops ITS next candidate, so the long test is issued for many lanes at once instead of once per
+// large primitive for the few lanes that touch that one.
+__device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, unsigned mask, Counters &cnt) {
     T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
+    unsigned cand = 0;
     for (int i = 0; i < s.num_large; i++) {
         float tn;
         RTB_COUNT(cnt, box);
-        if (box_test(__ldg(s.large_boxes + 2 * i), __ldg(s.large_boxes + 2 * i + 1), r, T.best.t * 1.0001f, tn))
+        if (box_test(__ldg(s.large_boxes + 2 * i), __ldg(s.large_boxes + 2 * i + 1), r, RTB_INF_F, tn)) cand |= 1u << i;
+    }
+    while (__any_sync(mask, cand != 0)) {
+        if (cand) {
+            int i = __ffs(cand) - 1;
+            cand &= cand - 1;
             test_leaf(s, r, __ldg(s.large_refs + i), T.best, cnt);
+        }
     }
     T.sp = 0;
     T.leaf = 0;
     T.cur = s.num_bvh_prims > 0 ? s.root_ref : RTB_DONE;
 }
 
-// Advance the ray through the LBVH: "while-while" traversal with postponed leaves -- every lane
-// walks internal nodes until it holds a leaf, then the warp tests leaves together, so the (long)
-// primitive test is issued for many lanes at once.  Returns when the ray is finished or when fewer
-// than `min_active` lanes of the warp are still traversing (0 = run to completion).
-__device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, int min_active, Counters &cnt) {
+// Advance the ray through the LBVH: warp-synchronous "while-while" traversal with postponed
+// leaves.  All lanes of `mask` move through the two phases together (the ballots are the
+// reconvergence points, so independent thread scheduling cannot let early lanes run ahead into a
+// leaf test on their own):
+//   NODE phase  lanes whose cursor is an internal node take one step per iteration; a lane that
+//               reaches its first leaf postpones it and keeps walking; the phase ends when at most
+//               `node_exit` lanes are still looking for their first leaf;
+//   LEAF phase  every lane that holds a leaf tests it (the long primitive test is issued once for
+//               all of them).
+// Returns when no lane has work left, or when at least `quota` lanes of the mask have finished
+// their ray (they go and shade / fetch new rays while the others keep their place in the tree;
+// quota <= 0 = run to completion).
+__device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int node_exit,
+                                         Counters &cnt) {
     int cur = T.cur, leaf = T.leaf, sp = T.sp;
     Best best = T.best;
-    while (cur != RTB_DONE || leaf < 0) {
-        while (cur >= 0 && cur != RTB_DONE) {
-            const float4 *N = s.nodes + 4 * cur;
-            float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
-            // relative slack on the distance cull: a primitive's own t carries more rounding than
-            // the box planes do (cancellation in Moller-Trumbore), so keep boxes that start a
-            // hair beyond the current best
-            float limit = best.t * 1.0001f;
-            float n0, n1;
-            RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
-            bool h0 = box_test(lo0, hi0, r, limit, n0);
-            bool h1 = box_test(lo1, hi1, r, limit, n1);
-            int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
-            if (h0 && h1) {
-                bool first0 = n0 <= n1;
-                cur = first0 ? r0 : r1;
-                if (sp < RTB_STACK) T.stack[sp++] = first0 ? r1 : r0;
-            } else if (h0) {
-                cur = r0;
-            } else if (h1) {
-                cur = r1;
-            } else {
-                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+    for (;;) {
+        for (;;) {
+            bool walk = cur >= 0 && cur != RTB_DONE;
+            unsigned searching = __ballot_sync(mask, walk && leaf == 0);
+            if (!searching) break;
+            if (__popc(searching) <= node_exit && __any_sync(mask, leaf < 0)) break;
+            if (walk) {
+                const float4 *N = s.nodes + 4 * cur;
+                float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
+                // relative slack on the distance cull: a primitive's own t carries more rounding
+                // than the box planes do (cancellation in Moller-Trumbore), so keep boxes that
+                // start a hair beyond the current best
+                float limit = best.t * 1.0001f;
+                float n0, n1;
+                RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
+                bool h0 = box_test(lo0, hi0, r, limit, n0);
+                bool h1 = box_test(lo1, hi1, r, limit, n1);
+                int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
+                if (h0 && h1) {
+                    bool first0 = n0 <= n1;
+                    cur = first0 ? r0 : r1;
+                    if (sp < RTB_STACK) T.stack[sp++] = first0 ? r1 : r0;
+                } else if (h0) {
+                    cur = r0;
+                } else if (h1) {
+                    cur = r1;
+                } else {
+                    cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+                }
+                if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
+                    leaf = cur;
+                    cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+                }
             }
-            if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
-                leaf = cur;
-                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
-            }
-            if (!__any_sync(__activemask(), leaf == 0)) break;  // every lane here holds a leaf
         }
-        while (leaf < 0) {
+        if (leaf < 0) {
             test_leaf(s, r, leaf, best, cnt);
             leaf = 0;
             if (cur < 0) {  // a second leaf was reached while the first was pending
@@ -224,16 +249,18 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                 cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
             }
         }
-        if (__popc(__activemask()) < min_active) break;  // too few lanes left: let the others refill
+        unsigned alive = __ballot_sync(mask, cur != RTB_DONE || leaf < 0);
+        if (!alive) break;
+        if (quota > 0 && __popc(mask & ~alive) >= quota) break;
     }
     T.cur = cur; T.leaf = leaf; T.sp = sp; T.best = best;
 }
 
-// closest hit over the whole scene through the LBVH, in one go
-__device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, Counters &cnt) {
+// closest hit over the whole scene through the LBVH, in one go; `mask` = the calling lanes
+__device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, unsigned mask, Counters &cnt) {
     Trav T;
-    trav_begin(s, r, T, cnt);
-    trav_run(s, r, T, 0, cnt);
+    trav_begin(s, r, T, mask, cnt);
+    trav_run(s, r, T, mask, 0, 0, cnt);
     return T.best;
 }
 

@@ -32,6 +32,14 @@ if __name__ == "__main__":
         run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 16})
         run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 32})
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "sweep2":
+        for r in (4, 8, 12, 16, 24):
+            for ne in (0, 2, 4, 8):
+                run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"refill": r, "node_exit": ne})
+        for r in (8, 16):
+            for ne in (0, 4):
+                run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": r, "node_exit": ne})
+        sys.exit(0)
     run("C1", 0, 0, 0, 1000, 800, 100, 5)
     run("C2", 5, 0, 0, 1920, 1080, 64, 8)
     run("C3", 0, 0, 0, 1920, 1080, 64, 8)

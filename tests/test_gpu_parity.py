@@ -79,8 +79,10 @@ def test_lbvh_equals_brute_force(tracer, sid, p0, p1):
 
 
 def _compare(img, ref):
+    # a path that takes a different discrete turn changes a pixel by O(radiance / spp); libm ulps in
+    # the continuous textures of scene 2 (sphere uv through asinf / acosf) change it by ~1e-8
     diff = np.abs(img - ref).max(axis=2)
-    differ = diff > 0
+    differ = diff > 1e-5
     rmse_all = float(np.sqrt(((img - ref) ** 2).mean()))
     return float(differ.mean()), rmse_all
 
