@@ -58,8 +58,17 @@ struct rtb_ctx {
     RtbCounters last_counters{};
     bool timing_pending = false;
 
+    // wavefront variant: per-pixel records, two queues, counters {n[0], n[1], fetch}
+    float4 *d_wf_state = nullptr;
+    int *d_wf_queue = nullptr;
+    unsigned int *d_wf_counts = nullptr;
+    size_t wf_slots = 0;
+    int wf_shade_per_sm = 0, wf_trav_per_sm = 0;
+
     // options
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_node_exit = 4;
+    int opt_kernel = 0;  // 0 = persistent megakernel, 1 = wavefront
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_node_exit = 4, opt_wf_refill = 8;
+    int opt_builder = 0, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
 };
@@ -340,7 +349,10 @@ int ensure_image(rtb_ctx *c) {
     return 0;
 }
 
+int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num);
+
 int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
+    if (c->opt_kernel == 1) return launch_frame_wavefront(c, time_ms, frame_num);
     RenderParams p;
     p.scene = c->d;
     std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
@@ -369,6 +381,73 @@ int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     cudaError_t e = c->opt_strict ? strict::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream)
                                   : fast::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream);
     if (e != cudaSuccess) return fail(c, "launching render kernel", cudaGetErrorString(e));
+    return 0;
+}
+
+// One frame through the wavefront kernels (rtb_wavefront.cuh): first wf_shade starts every pixel,
+// then spp * reflection_limit iterations of {wf_traverse, wf_shade}; an iteration advances every
+// live pixel by one path segment, so after the last one every pixel has written its result.
+int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
+    int local_rows = shard_local_rows(c, c->shard_rank);
+    size_t slots = (size_t)c->width * local_rows;
+    if (slots == 0) return 0;
+    if (c->rd.reflection_limit > 255) return fail(c, "render", "the wavefront kernels pack the bounce index in 8 bits (reflection_limit <= 255)");
+    if ((long long)c->rd.rays_per_pixel >= (1 << 24)) return fail(c, "render", "the wavefront kernels pack the sample index in 24 bits");
+    if (c->wf_slots < slots) {
+        if (c->d_wf_state) cudaFree(c->d_wf_state);
+        if (c->d_wf_queue) cudaFree(c->d_wf_queue);
+        c->d_wf_state = nullptr; c->d_wf_queue = nullptr; c->wf_slots = 0;
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_state, slots * 6 * sizeof(float4)), "allocating wavefront state");
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_queue, slots * 2 * sizeof(int)), "allocating wavefront queues");
+        c->wf_slots = slots;
+    }
+    if (!c->d_wf_counts) RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_counts, 4 * sizeof(unsigned int)), "allocating wavefront counters");
+    if (c->wf_shade_per_sm == 0) {
+        cudaError_t e = c->opt_strict ? strict::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm) : fast::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm);
+        if (e != cudaSuccess || c->wf_shade_per_sm <= 0 || c->wf_trav_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
+    }
+    WfParams p;
+    p.scene = c->d;
+    std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
+    p.rd.rays_per_pixel = c->rd.rays_per_pixel;
+    p.rd.reflection_limit = c->rd.reflection_limit;
+    p.rd.antialias = c->rd.antialias;
+    p.rd.sky[0] = c->rd.sky_colour.x; p.rd.sky[1] = c->rd.sky_colour.y; p.rd.sky[2] = c->rd.sky_colour.z;
+    p.width = c->width; p.height = c->height;
+    p.time_ms = time_ms; p.frame_num = frame_num;
+    p.prev = c->d_image; p.out = c->d_image;
+    p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
+    p.local_rows = local_rows;
+    float4 *st = c->d_wf_state;
+    p.st.A = st; p.st.B = st + slots; p.st.C = st + 2 * slots; p.st.O = st + 3 * slots; p.st.D = st + 4 * slots; p.st.H = st + 5 * slots;
+    int *queue[2] = {c->d_wf_queue, c->d_wf_queue + slots};
+    unsigned int *count[2] = {c->d_wf_counts, c->d_wf_counts + 1};
+    p.fetch = c->d_wf_counts + 2;
+    p.refill = c->opt_wf_refill < 1 ? 1 : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
+    p.node_exit = c->opt_node_exit < 0 ? 0 : (c->opt_node_exit > 31 ? 31 : c->opt_node_exit);
+    p.counters = c->opt_counters ? c->d_counters : nullptr;
+    const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
+    int shade_blocks = (int)std::min<size_t>((slots + 255) / 256, (size_t)c->num_sms * c->wf_shade_per_sm);
+    int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
+    int trav_blocks = c->num_sms * trav_per_sm;
+    RTB_CUDA(c, cudaMemsetAsync(c->d_wf_counts, 0, 4 * sizeof(unsigned int), c->stream), "resetting wavefront counters");
+    auto shade = [&](int first, int in, int out) {
+        p.first = first;
+        p.queue_in = queue[in]; p.n_in = count[in];
+        p.queue_out = queue[out]; p.n_out = count[out];
+        return strict_fp ? strict::launch_wf_shade(p, count_ops, shade_blocks, c->stream) : fast::launch_wf_shade(p, count_ops, shade_blocks, c->stream);
+    };
+    cudaError_t e = shade(1, 1, 0);
+    long long iterations = (long long)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
+    for (long long k = 0; k < iterations && e == cudaSuccess; k++) {
+        int in = (int)(k & 1), out = in ^ 1;
+        p.first = 0;
+        p.queue_in = queue[in]; p.n_in = count[in];
+        p.queue_out = queue[out]; p.n_out = count[out];
+        e = strict_fp ? strict::launch_wf_traverse(p, brute, count_ops, trav_blocks, c->stream) : fast::launch_wf_traverse(p, brute, count_ops, trav_blocks, c->stream);
+        if (e == cudaSuccess) e = shade(0, in, out);
+    }
+    if (e != cudaSuccess) return fail(c, "launching wavefront kernels", cudaGetErrorString(e));
     return 0;
 }
 
@@ -440,6 +519,9 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_work) cudaFree(c->d_work);
     if (c->d_counters) cudaFree(c->d_counters);
+    if (c->d_wf_state) cudaFree(c->d_wf_state);
+    if (c->d_wf_queue) cudaFree(c->d_wf_queue);
+    if (c->d_wf_counts) cudaFree(c->d_wf_counts);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -616,7 +698,7 @@ int rtb_scene_commit(rtb_ctx *c) {
     float4 *nodes = nullptr;
     int root = 0;
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "timing LBVH build");
-    RTB_CUDA(c, lbvh_build(in, &nodes, &root, c->stream), "building LBVH");
+    RTB_CUDA(c, lbvh_build(in, &nodes, &root, c->stream, c->opt_builder, c->opt_ploc_radius), "building LBVH");
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "timing LBVH build");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "building LBVH");
     float ms = 0;
@@ -836,12 +918,19 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     std::string k(key);
     if (k == "counters") c->opt_counters = value;
     else if (k == "traversal") c->opt_traversal = value;
-    else if (k == "strict_fp") c->opt_strict = value;
+    else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; }
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
+    else if (k == "builder") c->opt_builder = value;
+    else if (k == "ploc_radius") c->opt_ploc_radius = value;
     else if (k == "large_split") c->opt_large_split = value;          // takes effect at the next commit
     else if (k == "max_large") c->opt_max_large = value;
     else if (k == "refill") c->opt_refill = value;  // lanes waiting before a warp leaves the tree to shade
     else if (k == "node_exit") c->opt_node_exit = value;
+    else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
+    else if (k == "kernel") {
+        if (value != 0 && value != 1) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront");
+        c->opt_kernel = value;
+    }
     else if (k == "block_threads") {
         if (value != RTB_BLOCK_THREADS) return fail(c, "rtb_set_option", "block_threads is fixed at build time");
     } else if (k == "blocks_per_sm") c->opt_blocks_per_sm = value;

@@ -30,6 +30,31 @@ struct IdsParams {
     float *t;
 };
 
+// ---- wavefront variant (rtb_wavefront.cuh) -----------------------------------------------------
+struct WfState {
+    float4 *A, *B, *C, *O, *D, *H;
+};
+
+struct WfParams {
+    DScene scene;
+    DCamera cam;
+    DRender rd;
+    int width, height;
+    int time_ms, frame_num;
+    const float *prev;
+    float *out;
+    int shard_rank, shard_world, band_rows, local_rows;
+    WfState st;
+    const int *queue_in;        // live pixel slots of this iteration (nullptr = identity 0..n-1)
+    int *queue_out;             // live slots of the next iteration
+    const unsigned int *n_in;   // device counters
+    unsigned int *n_out;        // wf_shade: appended to; wf_traverse: zeroed for the next wf_shade
+    unsigned int *fetch;        // wf_traverse: next queue position to hand out (zeroed by wf_shade)
+    int first;                  // wf_shade: 1 = no hit to consume yet (start of the frame)
+    int refill, node_exit;
+    unsigned long long *counters;
+};
+
 struct LaunchConfig {
     int blocks, threads;
 };
@@ -39,6 +64,9 @@ struct LaunchConfig {
     cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st);    \
     cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st);                                \
     cudaError_t render_occupancy(int threads, int *blocks_per_sm);                                                  \
+    cudaError_t launch_wf_shade(const WfParams &p, bool count, int blocks, cudaStream_t st);                        \
+    cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
+    cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \
     }
 RTB_DECLARE_VARIANT(fast)
 RTB_DECLARE_VARIANT(strict)

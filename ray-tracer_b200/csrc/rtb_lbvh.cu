@@ -8,6 +8,7 @@
 #include "rtb_lbvh.h"
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstring>
 
 namespace rtb {
 namespace {
@@ -255,6 +256,127 @@ __global__ void pack_nodes_kernel(int n, const int *vals, const int *leaf_refs, 
     nodes[4 * i + 2] = olo; nodes[4 * i + 3] = ohi;
 }
 
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) ------------------------
+// Bottom-up agglomerative build over the Morton-sorted leaves: every round each cluster looks
+// `radius` positions left and right for the neighbour whose union with it has the smallest surface
+// area, mutual nearest neighbours merge into a new node, and the cluster array is compacted in
+// order.  The result is close to a full SAH build (large primitives stay near the root because
+// merging them is expensive), which the Karras split of the Morton codes is not.
+// Cluster i = {lo.xyz, ref} {hi.xyz, -} with ref a finished child reference (>= 0 node, < 0 leaf).
+constexpr int PLOC_T = 256;
+constexpr int PLOC_MAX_RADIUS = 32;
+
+__device__ __forceinline__ float union_half_area(float4 alo, float4 ahi, float4 blo, float4 bhi) {
+    float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x);
+    float dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y);
+    float dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void ploc_init_kernel(int n, const int *vals, const int *leaf_refs, const float4 *leaf_lo, const float4 *leaf_hi,
+                                 float4 *clo, float4 *chi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int v = vals[i];
+    float4 lo = leaf_lo[v], hi = leaf_hi[v];
+    lo.w = __int_as_float(leaf_refs[v]);
+    clo[i] = lo;
+    chi[i] = hi;
+}
+
+// nearest neighbour inside the window; ties go to the lower index (which guarantees that the
+// globally cheapest pair is mutual, so every round merges at least one pair)
+__global__ void ploc_nn_kernel(int n, int radius, const float4 *clo, const float4 *chi, int *nn) {
+    __shared__ float4 slo[PLOC_T + 2 * PLOC_MAX_RADIUS], shi[PLOC_T + 2 * PLOC_MAX_RADIUS];
+    int base = blockIdx.x * PLOC_T - radius;
+    for (int k = threadIdx.x; k < PLOC_T + 2 * radius; k += PLOC_T) {
+        int g = base + k;
+        if (g >= 0 && g < n) { slo[k] = clo[g]; shi[k] = chi[g]; }
+    }
+    __syncthreads();
+    int i = blockIdx.x * PLOC_T + threadIdx.x;
+    if (i >= n) return;
+    float4 lo = slo[threadIdx.x + radius], hi = shi[threadIdx.x + radius];
+    float best = 3.0e38f;
+    int best_j = -1;
+    for (int d = -radius; d <= radius; d++) {
+        int j = i + d;
+        if (d == 0 || j < 0 || j >= n) continue;
+        float a = union_half_area(lo, hi, slo[threadIdx.x + radius + d], shi[threadIdx.x + radius + d]);
+        if (a < best) { best = a; best_j = j; }
+    }
+    nn[i] = best_j;
+}
+
+// mutual nearest neighbours merge: the lower index keeps the new cluster, the higher one dies.
+// The node is written in its final traversal layout (both child boxes padded, refs in lo.w).
+__global__ void ploc_merge_kernel(int n, const int *nn, float4 *clo, float4 *chi, int *keep, float4 *nodes, int *node_counter) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int j = nn[i];
+    bool mutual = j >= 0 && nn[j] == i;
+    if (!mutual) { keep[i] = 1; return; }
+    if (i > j) { keep[i] = 0; return; }
+    float4 alo = clo[i], ahi = chi[i], blo = clo[j], bhi = chi[j];
+    int node = atomicAdd(node_counter, 1);
+    float4 olo, ohi;
+    padded(alo, ahi, __float_as_int(alo.w), olo, ohi);
+    nodes[4 * node] = olo; nodes[4 * node + 1] = ohi;
+    padded(blo, bhi, __float_as_int(blo.w), olo, ohi);
+    nodes[4 * node + 2] = olo; nodes[4 * node + 3] = ohi;
+    clo[i] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(node));
+    chi[i] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+    keep[i] = 1;
+}
+
+// order-preserving compaction in three steps: per-block counts, scan of the counts (one block),
+// scatter.  Blocks of PLOC_T clusters.
+__global__ void ploc_count_kernel(int n, const int *keep, int *block_count) {
+    int i = blockIdx.x * PLOC_T + threadIdx.x;
+    int c = __syncthreads_count(i < n && keep[i]);
+    if (threadIdx.x == 0) block_count[blockIdx.x] = c;
+}
+
+__global__ void ploc_scan_kernel(int num_blocks, int *block_count, int *total) {
+    __shared__ int part[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < num_blocks; base += 1024) {
+        int i = base + threadIdx.x;
+        int v = i < num_blocks ? block_count[i] : 0;
+        part[threadIdx.x] = v;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            int t = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+            __syncthreads();
+            part[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < num_blocks) block_count[i] = carry + part[threadIdx.x] - v;  // exclusive
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += part[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void ploc_scatter_kernel(int n, const int *keep, const int *block_offset, const float4 *clo, const float4 *chi,
+                                    float4 *clo_out, float4 *chi_out) {
+    __shared__ int warp_sum[PLOC_T / 32];
+    int i = blockIdx.x * PLOC_T + threadIdx.x;
+    bool k = i < n && keep[i];
+    unsigned int b = __ballot_sync(0xffffffffu, k);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warp_sum[warp] = __popc(b);
+    __syncthreads();
+    int off = block_offset[blockIdx.x];
+    for (int w = 0; w < warp; w++) off += warp_sum[w];
+    off += __popc(b & ((1u << lane) - 1u));
+    if (k) { clo_out[off] = clo[i]; chi_out[off] = chi[i]; }
+}
+
 __global__ void init_bounds_kernel(unsigned int *b) {
     if (threadIdx.x < 3) b[threadIdx.x] = 0xffffffffu;
     else if (threadIdx.x < 6) b[threadIdx.x] = 0u;
@@ -264,7 +386,7 @@ __global__ void init_bounds_kernel(unsigned int *b) {
 
 #define LBVH_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
-cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st) {
+cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st, int builder, int ploc_radius) {
     *nodes_out = nullptr;
     *root_ref = 0;
     const int n = in.num_prims;
@@ -285,6 +407,8 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
     unsigned int *hist = nullptr, *bounds = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *parent_internal = nullptr, *parent_leaf = nullptr, *flags = nullptr;
     int2 *children = nullptr;
+    float4 *clo2 = nullptr, *chi2 = nullptr;
+    int *block_count = nullptr;
     LBVH_CHECK(cudaMalloc(&leaf_lo, sizeof(float4) * n));
     LBVH_CHECK(cudaMalloc(&leaf_hi, sizeof(float4) * n));
     LBVH_CHECK(cudaMalloc(&node_lo, sizeof(float4) * n));
@@ -312,18 +436,55 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
         unsigned long long *tk = keys; keys = keys2; keys2 = tk;
         int *tv = vals; vals = vals2; vals2 = tv;
     }
-    karras_kernel<<<B, T, 0, st>>>(n, keys, children, parent_internal, parent_leaf);
-    refit_kernel<<<B, T, 0, st>>>(n, vals, leaf_lo, leaf_hi, children, parent_internal, parent_leaf, node_lo, node_hi, flags);
-    pack_nodes_kernel<<<B, T, 0, st>>>(n, vals, in.leaf_refs, leaf_lo, leaf_hi, children, node_lo, node_hi, nodes);
+    if (builder == 1) {
+        // PLOC over the sorted leaves; cluster arrays ping-pong between (node_lo, node_hi) and (clo2, chi2)
+        int radius = ploc_radius < 1 ? 1 : (ploc_radius > PLOC_MAX_RADIUS ? PLOC_MAX_RADIUS : ploc_radius);
+        int max_blocks = (n + PLOC_T - 1) / PLOC_T;
+        LBVH_CHECK(cudaMalloc(&clo2, sizeof(float4) * n));
+        LBVH_CHECK(cudaMalloc(&chi2, sizeof(float4) * n));
+        LBVH_CHECK(cudaMalloc(&block_count, sizeof(int) * (max_blocks + 2)));
+        int *node_counter = block_count + max_blocks, *total = block_count + max_blocks + 1;
+        LBVH_CHECK(cudaMemsetAsync(node_counter, 0, sizeof(int), st));
+        float4 *clo = node_lo, *chi = node_hi, *clo_alt = clo2, *chi_alt = chi2;
+        int *nn = parent_internal, *keep = parent_leaf;
+        ploc_init_kernel<<<B, T, 0, st>>>(n, vals, in.leaf_refs, leaf_lo, leaf_hi, clo, chi);
+        int count = n;
+        while (count > 1) {
+            int blocks = (count + PLOC_T - 1) / PLOC_T;
+            ploc_nn_kernel<<<blocks, PLOC_T, 0, st>>>(count, radius, clo, chi, nn);
+            ploc_merge_kernel<<<blocks, PLOC_T, 0, st>>>(count, nn, clo, chi, keep, nodes, node_counter);
+            ploc_count_kernel<<<blocks, PLOC_T, 0, st>>>(count, keep, block_count);
+            ploc_scan_kernel<<<1, 1024, 0, st>>>(blocks, block_count, total);
+            ploc_scatter_kernel<<<blocks, PLOC_T, 0, st>>>(count, keep, block_count, clo, chi, clo_alt, chi_alt);
+            int next = 0;
+            LBVH_CHECK(cudaMemcpyAsync(&next, total, sizeof(int), cudaMemcpyDeviceToHost, st));
+            LBVH_CHECK(cudaStreamSynchronize(st));
+            if (next <= 0 || next >= count) { err = cudaErrorUnknown; goto done; }  // cannot happen: the cheapest pair is mutual
+            count = next;
+            float4 *t0 = clo; clo = clo_alt; clo_alt = t0;
+            t0 = chi; chi = chi_alt; chi_alt = t0;
+        }
+        float4 root;
+        LBVH_CHECK(cudaMemcpyAsync(&root, clo, sizeof(float4), cudaMemcpyDeviceToHost, st));
+        LBVH_CHECK(cudaStreamSynchronize(st));
+        int root_node;
+        std::memcpy(&root_node, &root.w, sizeof(int));
+        *root_ref = root_node;
+    } else {
+        karras_kernel<<<B, T, 0, st>>>(n, keys, children, parent_internal, parent_leaf);
+        refit_kernel<<<B, T, 0, st>>>(n, vals, leaf_lo, leaf_hi, children, parent_internal, parent_leaf, node_lo, node_hi, flags);
+        pack_nodes_kernel<<<B, T, 0, st>>>(n, vals, in.leaf_refs, leaf_lo, leaf_hi, children, node_lo, node_hi, nodes);
+        *root_ref = 0;
+    }
     LBVH_CHECK(cudaGetLastError());
     LBVH_CHECK(cudaStreamSynchronize(st));
     *nodes_out = nodes;
     nodes = nullptr;
-    *root_ref = 0;
 done:
     cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(node_lo); cudaFree(node_hi); cudaFree(nodes);
     cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2); cudaFree(hist); cudaFree(bounds);
     cudaFree(parent_internal); cudaFree(parent_leaf); cudaFree(flags); cudaFree(children);
+    cudaFree(clo2); cudaFree(chi2); cudaFree(block_count);
     return err;
 }
 

@@ -12,7 +12,9 @@ struct LbvhInput {
 };
 
 // Builds the tree on `st`.  *nodes_out: cudaMalloc'd (n-1)*4 float4 (caller frees), nullptr when n < 2.
-// *root_ref: 0 (internal node 0) or, for a single primitive, its leaf ref.
-cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st);
+// *root_ref: the root's child reference (an internal node index or, for a single primitive, its leaf ref).
+// builder: 0 = Karras hierarchy over the Morton codes (LBVH), 1 = PLOC (agglomerative, near-SAH
+// quality) with search radius `ploc_radius` over the same Morton order.
+cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st, int builder, int ploc_radius);
 
 }  // namespace rtb

@@ -155,10 +155,88 @@ template <bool BRUTE> __device__ __forceinline__ Best trace(const DScene &s, con
 }
 
 // local row index -> global row for the row-cyclic band sharding (SURVEY.md 8(e) partitioning A)
-__device__ __forceinline__ int shard_row(const RenderParams &p, int local_row) {
-    if (p.shard_world <= 1) return local_row;
-    int band = local_row / p.band_rows, within = local_row - band * p.band_rows;
-    return (band * p.shard_world + p.shard_rank) * p.band_rows + within;
+__device__ __forceinline__ int shard_row(int rank, int world, int band_rows, int local_row) {
+    if (world <= 1) return local_row;
+    int band = local_row / band_rows, within = local_row - band * band_rows;
+    return (band * world + rank) * band_rows + within;
+}
+
+// ---- per-pixel path state (what the reference keeps on the thread's stack across the spp and
+// bounce loops, raytracer.cu:67-113) -- shared by the megakernel and the wavefront kernels so that
+// both evaluate the same expressions in the same order ----------------------------------------
+struct Path {
+    uint32_t rng;      // per pixel, carried from sample to sample (raytracer.cu:127-129)
+    int sample, bounce;
+    V3 thr, col, acc;  // ray_colour, final_colour of trace_ray (:68-69); sum over samples (:102-105)
+    float cur_n;       // Ray::current_refractive_index
+};
+
+struct FrameConsts {
+    int spp, limit;
+    bool aa;
+    V3 sky, cam_o;
+};
+
+__device__ __forceinline__ FrameConsts frame_consts(const DRender &rd, const DCamera &cam) {
+    FrameConsts f;
+    f.spp = rd.rays_per_pixel; f.limit = rd.reflection_limit; f.aa = rd.antialias != 0;
+    f.sky = v3(rd.sky[0], rd.sky[1], rd.sky[2]);
+    f.cam_o = v3(cam.cam_pos[0], cam.cam_pos[1], cam.cam_pos[2]);
+    return f;
+}
+
+// raytracer.cu:74-91 for a ray whose closest hit is `best`: sky on a miss, else scatter + light /
+// throughput; closes the sample when the path ends.  Returns true when the segment hit something.
+__device__ __forceinline__ bool path_shade(const DScene &s, const FrameConsts &f, Ray &ray, const Best &best, Path &P) {
+    bool end_sample, hit = best.code >= 0;
+    if (!hit) {
+        P.col = P.col + f.sky * P.thr;
+        end_sample = true;
+    } else {
+        Surface sf;
+        make_surface(s, ray, best, sf);
+        const DMaterial &m = s.materials[sf.material];
+        int mtype = __ldg(&m.type);
+        if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), P.cur_n, P.rng);
+        else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), P.rng);
+        if (mtype == 1) P.col = P.col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * P.thr;
+        else P.thr = P.thr * texture_colour(s, m, sf.u, sf.v);
+        P.bounce++;
+        end_sample = P.bounce >= f.limit;
+    }
+    if (end_sample) {
+        P.acc = P.acc + P.col;
+        P.sample++;
+        P.bounce = 0;
+    }
+    return hit;
+}
+
+__device__ __forceinline__ void path_begin_pixel(Path &P, int array_index, int time_ms) {
+    P.rng = rng_seed(array_index, time_ms);
+    P.acc = v3(0, 0, 0);
+    P.sample = 0;
+    P.bounce = 0;
+}
+
+// get_ray_colour's tail, raytracer.cu:107-112: mean over the samples, then the progressive mean
+__device__ __forceinline__ void path_write_pixel(const Path &P, int spp, int frame_num, const float *prev, float *out, int array_index) {
+    V3 colour = P.acc / (float)spp;
+    V3 previous = v3(prev[array_index], prev[array_index + 1], prev[array_index + 2]);
+    V3 previous_sum = previous * (float)frame_num;
+    V3 res = (colour + previous_sum) / (float)(frame_num + 1);
+    out[array_index] = res.x;
+    out[array_index + 1] = res.y;
+    out[array_index + 2] = res.z;
+}
+
+// trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
+__device__ __forceinline__ void path_begin_sample(const FrameConsts &f, V3 pdir, Ray &ray, Path &P) {
+    ray.o = f.cam_o;
+    change_direction(ray, pdir);
+    P.cur_n = 1;
+    P.thr = v3(1, 1, 1);
+    P.col = v3(0, 0, 0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -181,10 +259,7 @@ __device__ __forceinline__ int shard_row(const RenderParams &p, int local_row) {
 template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_megakernel(const RenderParams p) {
     const DScene &s = p.scene;
-    const int spp = p.rd.rays_per_pixel, limit = p.rd.reflection_limit;
-    const bool aa = p.rd.antialias != 0;
-    const V3 sky = v3(p.rd.sky[0], p.rd.sky[1], p.rd.sky[2]);
-    const V3 cam_o = v3(p.cam.cam_pos[0], p.cam.cam_pos[1], p.cam.cam_pos[2]);
+    const FrameConsts f = frame_consts(p.rd, p.cam);
     const int tiles_x = (p.width + 7) >> 3, tiles_y = (p.local_rows + 3) >> 2;
     const unsigned int total = (unsigned int)tiles_x * tiles_y * 32u;
     const unsigned int FULL = 0xffffffffu;
@@ -200,13 +275,12 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     bool pending = false;  // a finished ray whose hit has not been shaded yet
     bool fresh = false;    // a new ray that has not entered the tree yet
     int array_index = -1;  // (y * W + x) * 3 of the pixel this lane owns, -1 = none
-    uint32_t rng = 0;
-    int sample = 0, bounce = 0;
+    Path P;
+    P.rng = 0; P.sample = 0; P.bounce = 0; P.cur_n = 1;
+    P.thr = v3(1, 1, 1); P.col = v3(0, 0, 0); P.acc = v3(0, 0, 0);
     V3 pdir = v3(0, 0, 1);
     Ray ray;
-    ray.o = cam_o; ray.d = pdir; ray.inv = pdir;
-    V3 thr = v3(1, 1, 1), col = v3(0, 0, 0), acc = v3(0, 0, 0);
-    float cur_n = 1;
+    ray.o = f.cam_o; ray.d = pdir; ray.inv = pdir;
     Trav T;
     T.cur = RTB_DONE; T.leaf = 0; T.sp = 0;
     T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
@@ -220,29 +294,8 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
             if (mode == WAITING) {
                 if (pending) {  // raytracer.cu:74-91 for the ray that just finished
                     pending = false;
-                    if (COUNT) n_seg++;
-                    bool end_sample;
-                    if (T.best.code < 0) {
-                        col = col + sky * thr;
-                        end_sample = true;
-                    } else {
-                        if (COUNT) n_hit++;
-                        Surface sf;
-                        make_surface(s, ray, T.best, sf);
-                        const DMaterial &m = s.materials[sf.material];
-                        int mtype = __ldg(&m.type);
-                        if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), cur_n, rng);
-                        else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), rng);
-                        if (mtype == 1) col = col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * thr;
-                        else thr = thr * texture_colour(s, m, sf.u, sf.v);
-                        bounce++;
-                        end_sample = bounce >= limit;
-                    }
-                    if (end_sample) {
-                        acc = acc + col;
-                        sample++;
-                        bounce = 0;
-                    }
+                    bool hit = path_shade(s, f, ray, T.best, P);
+                    if (COUNT) { n_seg++; n_hit += hit; }
                 }
                 // advance the state machine until this lane holds a ray to trace (or runs dry)
                 for (;;) {
@@ -253,40 +306,26 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
                         int x = (int)(tile % tiles_x) * 8 + (int)(within & 7u);
                         int ly = (int)(tile / tiles_x) * 4 + (int)(within >> 3);
                         if (x >= p.width || ly >= p.local_rows) continue;
-                        int y = shard_row(p, ly);
+                        int y = shard_row(p.shard_rank, p.shard_world, p.band_rows, ly);
                         if (y >= p.height) continue;
                         array_index = (y * p.width + x) * 3;  // raytracer.cu:123
-                        rng = rng_seed(array_index, p.time_ms);
+                        path_begin_pixel(P, array_index, p.time_ms);
                         pdir = primary_direction(p.cam, x, y);
-                        acc = v3(0, 0, 0);
-                        sample = 0;
-                        bounce = 0;
                     }
-                    if (bounce == 0) {
-                        if (sample >= spp) {  // get_ray_colour, raytracer.cu:107-112
-                            V3 colour = acc / (float)spp;
-                            V3 previous = v3(p.prev[array_index], p.prev[array_index + 1], p.prev[array_index + 2]);
-                            V3 previous_sum = previous * (float)p.frame_num;
-                            V3 res = (colour + previous_sum) / (float)(p.frame_num + 1);
-                            p.out[array_index] = res.x;
-                            p.out[array_index + 1] = res.y;
-                            p.out[array_index + 2] = res.z;
+                    if (P.bounce == 0) {
+                        if (P.sample >= f.spp) {
+                            path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
                             array_index = -1;
                             continue;
                         }
-                        // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
-                        ray.o = cam_o;
-                        change_direction(ray, pdir);
-                        cur_n = 1;
-                        thr = v3(1, 1, 1);
-                        col = v3(0, 0, 0);
+                        path_begin_sample(f, pdir, ray, P);
                         if (COUNT) n_samples++;
-                        if (limit <= 0) { sample++; continue; }
+                        if (f.limit <= 0) { P.sample++; continue; }
                     }
                     break;  // a ray is ready
                 }
                 if (mode != IDLE) {
-                    if (aa) apply_antialias(ray, rng);
+                    if (f.aa) apply_antialias(ray, P.rng);
                     fresh = true;
                     mode = TRAVERSING;
                 }
@@ -370,6 +409,8 @@ cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st) 
 cudaError_t render_occupancy(int threads, int *blocks_per_sm) {
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_megakernel<false, false>, threads, 0);
 }
+
+#include "rtb_wavefront.cuh"
 
 }  // namespace RTB_NS
 }  // namespace rtb

@@ -188,6 +188,10 @@ __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &
     T.sp = 0;
     T.leaf = 0;
     T.cur = s.num_bvh_prims > 0 ? s.root_ref : RTB_DONE;
+    if (T.cur < 0) {  // a one-primitive tree: the root is a leaf
+        T.leaf = T.cur;
+        T.cur = RTB_DONE;
+    }
 }
 
 // Advance the ray through the LBVH: warp-synchronous "while-while" traversal with postponed
@@ -224,17 +228,14 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                 bool h0 = box_test(lo0, hi0, r, limit, n0);
                 bool h1 = box_test(lo1, hi1, r, limit, n1);
                 int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
-                if (h0 && h1) {
-                    bool first0 = n0 <= n1;
-                    cur = first0 ? r0 : r1;
-                    if (sp < RTB_STACK) T.stack[sp++] = first0 ? r1 : r0;
-                } else if (h0) {
-                    cur = r0;
-                } else if (h1) {
-                    cur = r1;
-                } else {
-                    cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
-                }
+                // branch-free cursor update (selects + one predicated push, one predicated pop):
+                // the four outcomes would otherwise run as four divergent paths
+                bool first0 = h0 && (!h1 || n0 <= n1);
+                int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
+                bool any = h0 || h1;  // invariant on exit: a leaf at the cursor implies a postponed leaf
+                if (h0 && h1 && sp < RTB_STACK) T.stack[sp++] = far;
+                cur = near;
+                if (!any) cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
                 if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
                     leaf = cur;
                     cur = sp > 0 ? T.stack[--sp] : RTB_DONE;

@@ -1,0 +1,205 @@
+// rtb_wavefront.cuh -- the wavefront variant of the render path (option "kernel" = 1).
+// Included by rtb_render.cuh inside namespace rtb::RTB_NS, after the shared path helpers.
+//
+// The megakernel keeps a pixel's whole state in one lane and has to run its two very different
+// halves -- shading (long, straight-line, RNG / libm heavy) and tree traversal (short, data
+// dependent loops) -- with whichever lanes of the warp happen to need them.  Here the halves are
+// separate kernels over a queue of live pixels:
+//
+//   wf_shade     one thread per live pixel: consume the closest hit of the pixel's current ray
+//                (raytracer.cu:74-91), advance the sample / bounce state machine, emit the next
+//                ray, or finish the pixel (raytracer.cu:107-112) and drop it from the queue
+//                (warp-ballot compaction, order preserving inside a warp);
+//   wf_traverse  persistent warps with per-lane dynamic fetch: a lane whose ray is finished
+//                stores the hit and pulls the next ray from the queue (cheap: two float4 loads),
+//                so the traversal loop runs with full warps.
+//
+// One iteration = one path segment of every live pixel.  The samples of a pixel stay strictly
+// serial (one live path per pixel), because the reference's RNG state is per pixel and carried
+// from sample to sample: the images are bit-identical to the megakernel's.
+//
+// Per-pixel record (6 float4 = 96 B, SoA by field, indexed by the pixel's local slot):
+//   A {thr.xyz, cur_n}   B {col.xyz, rng bits}   C {acc.xyz, sample << 8 | bounce}
+//   O {origin.xyz, -}    D {direction.xyz, -}    H {t, u, v, code}
+
+__device__ __forceinline__ void wf_slot_to_pixel(const WfParams &p, int slot, int &x, int &y) {
+    int ly = slot / p.width;
+    x = slot - ly * p.width;
+    y = shard_row(p.shard_rank, p.shard_world, p.band_rows, ly);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
+    const DScene &s = p.scene;
+    const FrameConsts f = frame_consts(p.rd, p.cam);
+    const unsigned int n = p.first ? (unsigned int)(p.width * p.local_rows) : *p.n_in;
+    const unsigned int lane = threadIdx.x & 31u;
+    unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.fetch = 0;  // for the traversal launch that follows
+    // whole warps walk the queue so that the ballot compaction below is converged
+    for (unsigned int base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
+        unsigned int i = base + lane;
+        bool live = i < n;
+        int slot = 0;
+        if (live) {
+            slot = p.queue_in && !p.first ? p.queue_in[i] : (int)i;
+            int x, y;
+            wf_slot_to_pixel(p, slot, x, y);
+            int array_index = (y * p.width + x) * 3;  // raytracer.cu:123
+            V3 pdir = primary_direction(p.cam, x, y);
+            Path P;
+            Ray ray;
+            if (p.first) {
+                path_begin_pixel(P, array_index, p.time_ms);
+                P.cur_n = 1; P.thr = v3(1, 1, 1); P.col = v3(0, 0, 0);
+                ray.o = f.cam_o; ray.d = pdir; ray.inv = pdir;
+            } else {
+                float4 a = p.st.A[slot], b = p.st.B[slot], c = p.st.C[slot], o = p.st.O[slot], d = p.st.D[slot], h = p.st.H[slot];
+                P.thr = v3(a.x, a.y, a.z); P.cur_n = a.w;
+                P.col = v3(b.x, b.y, b.z); P.rng = __float_as_uint(b.w);
+                P.acc = v3(c.x, c.y, c.z);
+                unsigned int sb = __float_as_uint(c.w);
+                P.sample = (int)(sb >> 8); P.bounce = (int)(sb & 255u);
+                ray.o = v3(o.x, o.y, o.z);
+                ray.d = v3(d.x, d.y, d.z);
+                ray.inv = ray.d;  // never read here: every direction change recomputes it (ray.cu:198-202)
+                Best best;
+                best.t = h.x; best.u = h.y; best.v = h.z; best.code = __float_as_int(h.w);
+                bool hit = path_shade(s, f, ray, best, P);
+                if (COUNT) { n_seg++; n_hit += hit; }
+            }
+            // advance until the pixel holds a ray to trace, or is finished
+            for (;;) {
+                if (P.bounce == 0) {
+                    if (P.sample >= f.spp) {
+                        path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
+                        live = false;
+                        break;
+                    }
+                    path_begin_sample(f, pdir, ray, P);
+                    if (COUNT) n_samples++;
+                    if (f.limit <= 0) { P.sample++; continue; }
+                }
+                break;
+            }
+            if (live) {
+                if (f.aa) apply_antialias(ray, P.rng);
+                p.st.A[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, P.cur_n);
+                p.st.B[slot] = make_float4(P.col.x, P.col.y, P.col.z, __uint_as_float(P.rng));
+                p.st.C[slot] = make_float4(P.acc.x, P.acc.y, P.acc.z, __uint_as_float(((unsigned int)P.sample << 8) | (unsigned int)P.bounce));
+                p.st.O[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.f);
+                p.st.D[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+            }
+        }
+        // compaction: the survivors of this warp go to consecutive queue positions, in order
+        unsigned int alive = __ballot_sync(0xffffffffu, live);
+        unsigned int pos = 0;
+        if (lane == 0 && alive) pos = atomicAdd(p.n_out, (unsigned int)__popc(alive));
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+        if (live) p.queue_out[pos + __popc(alive & ((1u << lane) - 1u))] = slot;
+    }
+    if (COUNT && p.counters) {
+        atomicAdd(p.counters + 0, n_seg);
+        atomicAdd(p.counters + 1, n_hit);
+        atomicAdd(p.counters + 5, n_samples);
+    }
+}
+
+// Persistent traversal: every lane owns one ray at a time; finished lanes store their hit and
+// fetch the next ray as soon as `refill` of them are waiting (or nobody traverses any more).
+template <bool BRUTE, bool COUNT>
+__global__ void __launch_bounds__(RTB_BLOCK_THREADS, 6) wf_traverse_kernel(const WfParams p) {
+    const DScene &s = p.scene;
+    const unsigned int FULL = 0xffffffffu;
+    const unsigned int n = *p.n_in;
+    const unsigned int lane = threadIdx.x & 31u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.n_out = 0;  // the counter the next wf_shade appends to
+    Counters cnt;
+    cnt.box = cnt.tri = cnt.sph = 0;
+    Ray ray;
+    ray.o = v3(0, 0, 0); ray.d = v3(0, 0, 1); ray.inv = ray.d;
+    Trav T;
+    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0;
+    T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
+    int slot = -1;           // the ray this lane owns, -1 = none
+    bool exhausted = false;  // the queue has nothing left (warp-uniform)
+    for (;;) {
+        bool busy = slot >= 0 && !trav_done(T);
+        unsigned int busy_mask = __ballot_sync(FULL, busy);
+        int free_lanes = 32 - __popc(busy_mask);
+        if (!exhausted && (free_lanes >= p.refill || !busy_mask)) {
+            // finished lanes store their result ...
+            if (slot >= 0 && !busy) {
+                p.st.H[slot] = make_float4(T.best.t, T.best.u, T.best.v, __int_as_float(T.best.code));
+                slot = -1;
+            }
+            // ... and take the next rays of the queue
+            unsigned int want = __ballot_sync(FULL, slot < 0);
+            unsigned int pos = 0;
+            if (lane == 0) pos = atomicAdd(p.fetch, (unsigned int)__popc(want));
+            pos = __shfl_sync(FULL, pos, 0);
+            unsigned int mine = pos + __popc(want & ((1u << lane) - 1u));
+            bool fresh = slot < 0 && mine < n;
+            if (pos + __popc(want) >= n) exhausted = true;
+            if (fresh) {
+                slot = p.queue_in ? p.queue_in[mine] : (int)mine;
+                float4 o = p.st.O[slot], d = p.st.D[slot];
+                ray.o = v3(o.x, o.y, o.z);
+                ray.d = v3(d.x, d.y, d.z);
+                ray.inv = v3(1 / d.x, 1 / d.y, 1 / d.z);  // ray.cu:198-202
+            }
+            unsigned int starting = __ballot_sync(FULL, fresh);
+            if (fresh) {
+                if (BRUTE) {
+                    T.best = trace_brute(s, ray, cnt);
+                    T.cur = RTB_DONE; T.leaf = 0;
+                } else {
+                    trav_begin(s, ray, T, starting, cnt);
+                }
+            }
+            busy = slot >= 0 && !trav_done(T);
+            busy_mask = __ballot_sync(FULL, busy);
+        }
+        if (!busy_mask) {
+            if (slot >= 0) {  // rays that ended inside trav_begin (or brute force)
+                p.st.H[slot] = make_float4(T.best.t, T.best.u, T.best.v, __int_as_float(T.best.code));
+                slot = -1;
+            }
+            if (exhausted) break;
+            continue;
+        }
+        if (busy) {
+            // while the queue has rays, leave the tree when `refill` lanes are free; afterwards run to the end
+            int quota = exhausted ? 0 : p.refill - (32 - __popc(busy_mask));
+            if (!BRUTE) trav_run(s, ray, T, busy_mask, exhausted ? 0 : (quota < 1 ? 1 : quota), p.node_exit, cnt);
+        }
+    }
+    if (COUNT && p.counters) {
+        atomicAdd(p.counters + 2, cnt.box);
+        atomicAdd(p.counters + 3, cnt.tri);
+        atomicAdd(p.counters + 4, cnt.sph);
+    }
+}
+
+cudaError_t launch_wf_shade(const WfParams &p, bool count, int blocks, cudaStream_t st) {
+    if (count) wf_shade_kernel<true><<<blocks, 256, 0, st>>>(p);
+    else wf_shade_kernel<false><<<blocks, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {
+    if (brute) {
+        if (count) wf_traverse_kernel<true, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+    } else {
+        if (count) wf_traverse_kernel<false, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm) {
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false>, 256, 0);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false>, RTB_BLOCK_THREADS, 0);
+}

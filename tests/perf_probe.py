@@ -32,6 +32,37 @@ if __name__ == "__main__":
         run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 16})
         run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 32})
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "sweep4":
+        C3 = ("C3", 0, 0, 0, 1920, 1080, 32, 8)
+        run(*C3, opts={"kernel": 0})
+        run(*C3, opts={"kernel": 1})
+        for b, ls, rad in ((1, 1, 16), (1, 0, 16), (1, 0, 8), (1, 0, 32), (0, 0, 16)):
+            for kern in (0, 1):
+                run(*C3, opts={"kernel": kern, "builder": b, "large_split": ls, "ploc_radius": rad})
+        for r in (2, 4, 16):
+            run(*C3, opts={"kernel": 1, "builder": 1, "large_split": 0, "wf_refill": r})
+        for ne in (0, 2, 8):
+            run(*C3, opts={"kernel": 1, "builder": 1, "large_split": 0, "node_exit": ne})
+        for kern in (0, 1):
+            for b, ls in ((0, 1), (1, 0)):
+                run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern, "builder": b, "large_split": ls})
+                run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern, "builder": b, "large_split": ls})
+                run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern, "builder": b, "large_split": ls})
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "sweep3":
+        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 0})
+        for r in (2, 4, 8, 16, 32):
+            for ne in (0, 4):
+                run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": r, "node_exit": ne})
+        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": 8, "node_exit": 4, "blocks_per_sm": 4})
+        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": 8, "node_exit": 4, "blocks_per_sm": 6})
+        run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": 0})
+        run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": 1})
+        run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": 0})
+        run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": 1})
+        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 0})
+        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1})
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "sweep2":
         for r in (4, 8, 12, 16, 24):
             for ne in (0, 2, 4, 8):

@@ -78,6 +78,90 @@ def test_lbvh_equals_brute_force(tracer, sid, p0, p1):
         assert (a == b).all()
 
 
+@pytest.mark.parametrize("sid,p0,p1", SCENES)
+def test_ploc_tree_equals_brute_force(tracer, sid, p0, p1):
+    """The PLOC builder (option builder=1), with and without the large-primitive list: the tree
+    shape must never change a result."""
+    scene = _scene(sid, p0, p1)
+    ref = None
+    try:
+        for builder, large in ((0, 1), (1, 1), (1, 0)):
+            tracer.set_option("builder", builder)
+            tracer.set_option("large_split", large)
+            tracer.setup(scene, W, H, 3, 6)
+            if ref is None:
+                tracer.set_option("traversal", 1)
+                ref = np.zeros((H, W, 3), np.float32)
+                tracer.render(ref, 0, 777)
+                ref_ids = tracer.primary_ids()
+                tracer.set_option("traversal", 0)
+            img = np.zeros((H, W, 3), np.float32)
+            tracer.render(img, 0, 777)
+            assert (img == ref).all(), f"builder {builder} large_split {large}"
+            for a, b in zip(tracer.primary_ids(), ref_ids):
+                assert (a == b).all()
+    finally:
+        tracer.set_option("builder", 0)
+        tracer.set_option("large_split", 1)
+        tracer.set_option("traversal", 0)
+
+
+@pytest.mark.parametrize("sid,p0,p1", SCENES)
+def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
+    """The wavefront kernels (option kernel=1) evaluate the same per-pixel function with the same
+    RNG order: images, progressive frames and counters are bit-identical to the megakernel's."""
+    scene = _scene(sid, p0, p1)
+    tracer.setup(scene, W, H, 3, 6)
+    out = []
+    try:
+        for kernel in (0, 1):
+            tracer.set_option("kernel", kernel)
+            tracer.set_option("counters", 1)
+            img = np.zeros((H, W, 3), np.float32)
+            f = tracer.render(img, 0, 4242)
+            c = tracer.counters()
+            f = tracer.render(img, f, 17)
+            out.append((img, f, c))
+    finally:
+        tracer.set_option("kernel", 0)
+        tracer.set_option("counters", 0)
+    assert out[0][1] == out[1][1] == 2
+    assert (out[0][0] == out[1][0]).all()
+    for k in ("segments", "hit_segments", "samples"):
+        assert out[0][2][k] == out[1][2][k]
+
+
+def test_wavefront_sharded_and_odd_sizes(tracer):
+    scene = _scene(3, 0, 0)
+    Ws, Hs = 203, 151
+    tracer.setup(scene, Ws, Hs, 2, 4)
+    full = np.zeros((Hs, Ws, 3), np.float32)
+    tracer.render(full, 0, 99)
+    try:
+        tracer.set_option("kernel", 1)
+        combined = np.zeros((Hs, Ws, 3), np.float32)
+        for rank in range(3):
+            tracer.set_shard(rank, 3, 5)
+            part = np.zeros((Hs, Ws, 3), np.float32)
+            tracer.render(part, 0, 99)
+            rows = rtb.shard_rows_host(Hs, rank, 3, 5)
+            combined[rows] = part[rows]
+        tracer.set_shard(0, 1, 8)
+        assert (combined == full).all()
+        # strict-fp variant and zero bounces
+        tracer.set_option("strict_fp", 1)
+        a = np.zeros((Hs, Ws, 3), np.float32)
+        tracer.render(a, 0, 5)
+        tracer.set_option("kernel", 0)
+        b = np.zeros((Hs, Ws, 3), np.float32)
+        tracer.render(b, 0, 5)
+        assert (a == b).all()
+    finally:
+        tracer.set_option("strict_fp", 0)
+        tracer.set_option("kernel", 0)
+        tracer.set_shard(0, 1, 8)
+
+
 def _compare(img, ref):
     # a path that takes a different discrete turn changes a pixel by O(radiance / spp); libm ulps in
     # the continuous textures of scene 2 (sphere uv through asinf / acosf) change it by ~1e-8
