@@ -232,6 +232,8 @@ def main():
     ap.add_argument("--band-rows", type=int, default=8)
     ap.add_argument("--ref-spp", type=int, default=8, help="spp per step of the reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront (library default)")
+    ap.add_argument("--builder", type=int, default=None, help="0 = Karras LBVH, 1 = PLOC (library default)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -257,7 +259,14 @@ def main():
 
     sid, p0, p1, W, H, spp, bounces = WORKLOADS[args.workload]
     scene = rtb.Scene(sid, p0, p1)
-    tr = rtb.Tracer(local_rank).setup(scene, W, H, spp, bounces)
+    tr = rtb.Tracer(local_rank)
+    if args.kernel is not None:
+        tr.set_option("kernel", args.kernel)
+    if args.builder is not None:
+        tr.set_option("builder", args.builder)
+    tr.setup(scene, W, H, spp, bounces)
+    kernel_kind = int(tr.info("kernel"))
+    per_frame = int(tr.info("launches_per_frame"))
     if world > 1:
         tr.set_shard(rank, world, args.band_rows)
     ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
@@ -315,7 +324,7 @@ def main():
             tr.reset()
             tr.render_device(1, 1000 + k)
             kev[k][1].record(ext)
-            launches += 1
+            launches += per_frame
             if world > 1:
                 tr.shard_pack(dense.data_ptr())
                 dist.all_gather_into_tensor(gathered, dense)
@@ -382,20 +391,24 @@ def main():
             "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "scene_id": sid, "width": W, "height": H, "spp_per_step": spp,
                        "bounces": bounces, "rays_per_step": rays_per_step, "segments_per_sample": cnt["segments"] / max(1, cnt["samples"]),
                        "sharding": "none" if world == 1 else f"row-cyclic bands of {args.band_rows} rows, NCCL all-gather per frame",
-                       "kernel": "persistent megakernel, LBVH", "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
+                       "kernel": ("wavefront: wf_shade + persistent wf_traverse per path segment" if kernel_kind == 1 else "persistent megakernel")
+                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
                        "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
                     "ms_per_step": e2e_ms / args.steps, "checksum": checksum},
-            "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak if fp32_peak else None,
+            "roofline": {"bound": "fp32", "kernel": "wf_traverse_kernel + wf_shade_kernel (all launches of a step)" if kernel_kind == 1 else "render_megakernel",
+                         "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak if fp32_peak else None,
                          "peak_kind": "measured FFMA microbenchmark on this GPU (rtb_measure_fp32_peak)", "peak_nominal": nominal_peak,
                          "frac_of_nominal": achieved_tf / nominal_peak, "traffic": None,
                          "flops_per_ray": fpr, "kernel_ms": kernel_ms,
                          "op_mix_per_ray": {"box": cnt["box_tests"] / cnt["segments"], "tri": cnt["tri_tests"] / cnt["segments"],
                                             "sphere": cnt["sphere_tests"] / cnt["segments"], "hit": cnt["hit_segments"] / cnt["segments"]},
                          "why": "no dense contraction and an L2-resident working set: the FP32 pipe bounds this path (SURVEY.md 8(d))",
-                         "hbm": {"achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
-                                 "peak_kind": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"}},
+                         "algorithmic_bytes": {"achieved": achieved_gbs, "unit": "GB/s", "peak_hbm": hbm_peak,
+                                               "note": "node/primitive bytes the traversal asks for (32 B per box, 48 B per triangle): served by L1/L2, NOT HBM traffic; "
+                                                       "measured dram bytes are in profiles/ (ncu)",
+                                               "peak_kind": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"}},
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg(args.workload, 1)

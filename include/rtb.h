@@ -188,6 +188,11 @@ int rtb_set_shard(rtb_ctx *ctx, int rank, int world, int band_rows);
 /* pack this rank's rows into a dense buffer / scatter a gathered [world][rows_per_rank] buffer back
  * into the full image (device pointers; rows_per_rank = rtb_shard_rows(ctx) padded to the max over ranks) */
 int rtb_shard_rows(rtb_ctx *ctx, int *rows_this_rank, int *rows_padded);
+/* the index arithmetic of the band sharding, usable without a context or a device: the image row of
+ * rank's local row (may be >= height in the padded tail), and how many rows of a height-row image
+ * rank owns */
+int rtb_shard_row_of(int local_row, int rank, int world, int band_rows);
+int rtb_shard_row_count(int height, int rank, int world, int band_rows);
 int rtb_shard_pack(rtb_ctx *ctx, void *dense_dev);
 int rtb_shard_unpack(rtb_ctx *ctx, const void *gathered_dev);
 

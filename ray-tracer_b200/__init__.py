@@ -24,7 +24,8 @@ class RtbError(RuntimeError):
 
 
 def _load(name):
-    path = os.path.join(_HERE, name)
+    # RTB_LIBRTB names an alternative build of librtb.so (A/B experiments of build-time knobs)
+    path = os.environ.get("RTB_LIBRTB") if name == "librtb.so" and os.environ.get("RTB_LIBRTB") else os.path.join(_HERE, name)
     if not os.path.exists(path):
         raise RtbError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                        f"(there is no CPU fallback for the render path)")
@@ -124,6 +125,8 @@ lib.rtb_stream.restype = _vp
 lib.rtb_last_device_ms.argtypes = [_vp, _fp]
 lib.rtb_set_shard.argtypes = [_vp, _i, _i, _i]
 lib.rtb_shard_rows.argtypes = [_vp, _ip, _ip]
+lib.rtb_shard_row_of.argtypes = [_i, _i, _i, _i]
+lib.rtb_shard_row_count.argtypes = [_i, _i, _i, _i]
 lib.rtb_shard_pack.argtypes = [_vp, _vp]
 lib.rtb_shard_unpack.argtypes = [_vp, _vp]
 lib.rtb_primary_ids.argtypes = [_vp, _vp, _vp, _vp]

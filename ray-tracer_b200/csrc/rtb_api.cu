@@ -56,6 +56,7 @@ struct rtb_ctx {
     unsigned int *d_work = nullptr;
     unsigned long long *d_counters = nullptr;
     RtbCounters last_counters{};
+    unsigned long long last_lane_stats[8] = {};  // traversal lane occupancy of the last counted render (wavefront)
     bool timing_pending = false;
 
     // wavefront variant: per-pixel records, two queues, counters {n[0], n[1], fetch}
@@ -66,9 +67,9 @@ struct rtb_ctx {
     int wf_shade_per_sm = 0, wf_trav_per_sm = 0;
 
     // options
-    int opt_kernel = 0;  // 0 = persistent megakernel, 1 = wavefront
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_node_exit = 4, opt_wf_refill = 8;
-    int opt_builder = 0, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
+    int opt_kernel = 1;  // 0 = persistent megakernel, 1 = wavefront (the measured winner)
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_walk_min = 16, opt_wf_refill = 8;
+    int opt_builder = 1, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
 };
@@ -304,13 +305,7 @@ int flatten(rtb_ctx *c, Flat &f) {
 // ---- shard helpers ---------------------------------------------------------------------------------
 namespace {
 
-int shard_local_rows(const rtb_ctx *c, int rank) {
-    if (c->shard_world <= 1) return c->height;
-    int rows = 0;
-    for (int y = 0; y < c->height; y++)
-        if ((y / c->band_rows) % c->shard_world == rank) rows++;
-    return rows;
-}
+int shard_local_rows(const rtb_ctx *c, int rank) { return rtb_shard_row_count(c->height, rank, c->shard_world, c->band_rows); }
 
 __global__ void shard_pack_kernel(const float *image, float *dense, int width, int local_rows, int rank, int world, int band_rows, int height) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -366,7 +361,7 @@ int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
     p.refill = c->opt_refill < 1 ? 1 : (c->opt_refill > 32 ? 32 : c->opt_refill);
-    p.node_exit = c->opt_node_exit < 0 ? 0 : (c->opt_node_exit > 31 ? 31 : c->opt_node_exit);
+    p.walk_min = c->opt_walk_min < 1 ? 1 : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     p.work_counter = c->d_work;
     p.counters = c->opt_counters ? c->d_counters : nullptr;
     RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
@@ -424,7 +419,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     unsigned int *count[2] = {c->d_wf_counts, c->d_wf_counts + 1};
     p.fetch = c->d_wf_counts + 2;
     p.refill = c->opt_wf_refill < 1 ? 1 : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
-    p.node_exit = c->opt_node_exit < 0 ? 0 : (c->opt_node_exit > 31 ? 31 : c->opt_node_exit);
+    p.walk_min = c->opt_walk_min < 1 ? 1 : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     p.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
     int shade_blocks = (int)std::min<size_t>((slots + 255) / 256, (size_t)c->num_sms * c->wf_shade_per_sm);
@@ -435,7 +430,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
         p.first = first;
         p.queue_in = queue[in]; p.n_in = count[in];
         p.queue_out = queue[out]; p.n_out = count[out];
-        return strict_fp ? strict::launch_wf_shade(p, count_ops, shade_blocks, c->stream) : fast::launch_wf_shade(p, count_ops, shade_blocks, c->stream);
+        return strict_fp ? strict::launch_wf_shade(p, brute, count_ops, shade_blocks, c->stream) : fast::launch_wf_shade(p, brute, count_ops, shade_blocks, c->stream);
     };
     cudaError_t e = shade(1, 1, 0);
     long long iterations = (long long)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
@@ -482,6 +477,21 @@ extern "C" {
 
 int rtb_abi_version(void) { return RTB_ABI_VERSION; }
 
+int rtb_shard_row_of(int local_row, int rank, int world, int band_rows) {
+    if (world <= 1 || band_rows <= 0) return local_row;
+    int band = local_row / band_rows, within = local_row - band * band_rows;
+    return (band * world + rank) * band_rows + within;
+}
+
+int rtb_shard_row_count(int height, int rank, int world, int band_rows) {
+    if (world <= 1 || band_rows <= 0) return height;
+    if (rank < 0 || rank >= world) return 0;
+    int period = world * band_rows, full = height / period, rest = height - full * period;
+    int extra = rest - rank * band_rows;
+    extra = extra < 0 ? 0 : (extra > band_rows ? band_rows : extra);
+    return full * band_rows + extra;
+}
+
 const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
 int rtb_create(rtb_ctx **out, int device) {
@@ -500,7 +510,7 @@ int rtb_create(rtb_ctx **out, int device) {
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
     if (e == cudaSuccess) e = cudaMalloc((void **)&c->d_work, sizeof(unsigned int));
-    if (e == cudaSuccess) e = cudaMalloc((void **)&c->d_counters, 6 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&c->d_counters, 16 * sizeof(unsigned long long));
     if (e != cudaSuccess) {
         fail(nullptr, "rtb_create", cudaGetErrorString(e));
         rtb_destroy(c);
@@ -746,10 +756,11 @@ int rtb_scene_desc(rtb_ctx *c, RtbSceneDesc *out) {
 
 static int fetch_counters(rtb_ctx *c) {
     if (!c->opt_counters) return 0;
-    unsigned long long h[6];
+    unsigned long long h[16];
     RTB_CUDA(c, cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream), "reading counters");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "reading counters");
     c->last_counters = RtbCounters{h[0], h[1], h[2], h[3], h[4], h[5]};
+    for (int k = 0; k < 8; k++) c->last_lane_stats[k] = h[8 + k];
     return 0;
 }
 
@@ -759,7 +770,7 @@ int rtb_render(rtb_ctx *c, float *rgb_inout, int *frame_num_inout, int current_t
     if (check_ready(c) != 0) return 1;
     size_t bytes = c->image_floats * sizeof(float);
     RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_inout, bytes, cudaMemcpyHostToDevice, c->stream), "copying previous render");
-    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream), "clearing counters");
+    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream), "clearing counters");
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
     if (launch_frame(c, current_time_ms, *frame_num_inout) != 0) return 1;
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "render");
@@ -775,7 +786,7 @@ int rtb_render_device(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) 
     if (!c || n_frames < 0) return 1;
     Bind b(c);
     if (check_ready(c) != 0) return 1;
-    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream), "clearing counters");
+    if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream), "clearing counters");
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
     for (int k = 0; k < n_frames; k++) {
         if (launch_frame(c, time0_ms + k * time_step_ms, c->frame_num) != 0) return 1;
@@ -925,7 +936,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "large_split") c->opt_large_split = value;          // takes effect at the next commit
     else if (k == "max_large") c->opt_max_large = value;
     else if (k == "refill") c->opt_refill = value;  // lanes waiting before a warp leaves the tree to shade
-    else if (k == "node_exit") c->opt_node_exit = value;
+    else if (k == "walk_min") c->opt_walk_min = value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
     else if (k == "kernel") {
         if (value != 0 && value != 1) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront");
@@ -974,6 +985,11 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "num_nodes") *value = c->d.num_bvh_prims > 1 ? c->d.num_bvh_prims - 1 : 0;
     else if (k == "num_large") *value = c->d.num_large;
     else if (k == "build_ms") *value = c->build_ms;
+    else if (k == "kernel") *value = c->opt_kernel;
+    else if (k == "builder") *value = c->opt_builder;
+    else if (k == "launches_per_frame")  // kernels of ONE frame: megakernel 1; wavefront 1 + 2 * spp * bounces
+        *value = c->opt_kernel == 1 ? 1.0 + 2.0 * (double)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit) : 1.0;
+    else if (k.rfind("lane_stat", 0) == 0 && k.size() == 10 && k[9] >= '0' && k[9] <= '7') *value = (double)c->last_lane_stats[k[9] - '0'];
     else if (k == "scene_bytes") *value = (double)c->scene_bytes;
     else if (k == "culled_tris") *value = c->culled_tris;
     else if (k == "num_sms") *value = c->num_sms;

@@ -17,7 +17,7 @@ struct RenderParams {
     int shard_rank, shard_world, band_rows;
     int local_rows;                  // rows owned by this rank
     int refill;                      // SHADE phase starts when this many lanes of a warp wait (1..32)
-    int node_exit;                   // NODE phase ends when at most this many lanes still look for a first leaf
+    int walk_min;                   // NODE phase wants this many walking lanes (rtb_trace.cuh)
     unsigned int *work_counter;      // zeroed before launch
     unsigned long long *counters;    // 6 slots (RtbCounters order) or nullptr
 };
@@ -51,7 +51,7 @@ struct WfParams {
     unsigned int *n_out;        // wf_shade: appended to; wf_traverse: zeroed for the next wf_shade
     unsigned int *fetch;        // wf_traverse: next queue position to hand out (zeroed by wf_shade)
     int first;                  // wf_shade: 1 = no hit to consume yet (start of the frame)
-    int refill, node_exit;
+    int refill, walk_min;
     unsigned long long *counters;
 };
 
@@ -64,7 +64,7 @@ struct LaunchConfig {
     cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st);    \
     cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st);                                \
     cudaError_t render_occupancy(int threads, int *blocks_per_sm);                                                  \
-    cudaError_t launch_wf_shade(const WfParams &p, bool count, int blocks, cudaStream_t st);                        \
+    cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);                     \
     cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
     cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \
     }

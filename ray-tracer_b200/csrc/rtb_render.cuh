@@ -263,10 +263,10 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     const int tiles_x = (p.width + 7) >> 3, tiles_y = (p.local_rows + 3) >> 2;
     const unsigned int total = (unsigned int)tiles_x * tiles_y * 32u;
     const unsigned int FULL = 0xffffffffu;
-    const int refill = p.refill, node_exit = p.node_exit;
+    const int refill = p.refill, walk_min = p.walk_min;
 
     Counters cnt;
-    cnt.box = cnt.tri = cnt.sph = 0;
+    cnt = Counters{};
     unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
 
     // lane state
@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
         // leave the tree once `refill` lanes of the warp wait for the SHADE phase
         int quota = refill - __popc(__ballot_sync(FULL, mode == WAITING));
         if (mode == TRAVERSING) {
-            if (!BRUTE) trav_run(s, ray, T, tmask, quota < 1 ? 1 : quota, node_exit, cnt);
+            if (!BRUTE) trav_run(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
             if (trav_done(T)) {
                 mode = WAITING;
                 pending = true;
@@ -375,7 +375,7 @@ template <bool BRUTE> __global__ void primary_ids_kernel(const IdsParams p) {
     change_direction(ray, primary_direction(p.cam, x, y));
     Counters cnt;
 #ifdef RTB_COUNTERS
-    cnt.box = cnt.tri = cnt.sph = 0;
+    cnt = Counters{};
 #endif
     Best best = trace<BRUTE>(p.scene, ray, mask, cnt);
     size_t i = (size_t)y * p.width + x;

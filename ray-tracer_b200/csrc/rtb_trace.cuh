@@ -19,11 +19,17 @@ struct Best {
 #ifdef RTB_COUNTERS
 struct Counters {
     unsigned long long box, tri, sph;
+    // lane-occupancy statistics of the traversal loops (counted by lane 0 of each warp):
+    // node_iters / leaf_iters = warp-level iterations, *_lanes = lanes doing useful work in them,
+    // blocked = lanes holding two leaves, done = lanes whose ray is finished, in node iterations
+    unsigned long long node_iters, node_lanes, node_blocked, node_done, leaf_iters, leaf_lanes, mask_lanes;
 };
 #define RTB_COUNT(c, f) ((c).f++)
+#define RTB_COUNT_N(c, f, n) ((c).f += (n))
 #else
 struct Counters {};
 #define RTB_COUNT(c, f)
+#define RTB_COUNT_N(c, f, n)
 #endif
 
 // ---- Triangle::hit, objects.cu:135-163 ---------------------------------------------------------
@@ -132,6 +138,9 @@ __device__ __forceinline__ void test_leaf(const DScene &s, const Ray &r, int ref
 // conservative, i.e. never reject a box that holds a primitive the exact tests above would accept
 // closer than `best`.  NaNs (0 * inf) are dropped by fminf/fmaxf, which widens the interval; the
 // final comparison carries a relative slack for the rounding of the six products.
+// (Measured and rejected: fma(plane, inv, -(o * inv)) halves the slab arithmetic, but the rounding
+// of o * inv is absolute, and covering it -- or switching flat axes off -- makes the rare rays that
+// are nearly parallel to an axis walk most of a large tree: 1M-triangle scene 1.4 G -> 6 M rays/s.)
 __device__ __forceinline__ bool box_test(float4 lo, float4 hi, const Ray &r, float limit, float &tnear) {
     float t1 = (lo.x - r.o.x) * r.inv.x, t2 = (hi.x - r.o.x) * r.inv.x;
     float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
@@ -164,14 +173,14 @@ struct Trav {
 
 __device__ __forceinline__ bool trav_done(const Trav &T) { return T.cur == RTB_DONE && T.leaf == 0; }
 
-// start a ray: large primitives first (the hit they give culls most of the tree), then point the
-// cursor at the root.  `mask` = the lanes of the warp that call this together.  The box tests run
-// converged (same address in every lane: broadcast loads) and only record which large primitives
-// the ray may touch; the primitive tests then run in a warp-synchronous loop in which every lane
-// pops ITS next candidate, so the long test is issued for many lanes at once instead of once per
-// large primitive for the few lanes that touch that one.
-__device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, unsigned mask, Counters &cnt) {
-    T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
+// The large primitives (walls, floors) are tested before the tree: the hit they give culls most of
+// it.  `mask` = the lanes of the warp that call this together.  The box tests run converged (same
+// address in every lane: broadcast loads) and only record which large primitives the ray may
+// touch; the primitive tests then run in a warp-synchronous loop in which every lane pops ITS next
+// candidate, so the long test is issued for many lanes at once instead of once per large primitive
+// for the few lanes that touch that one.
+__device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, Best &best, unsigned mask, Counters &cnt) {
+    best.t = RTB_INF_F; best.u = 0; best.v = 0; best.code = -1;
     unsigned cand = 0;
     for (int i = 0; i < s.num_large; i++) {
         float tn;
@@ -182,10 +191,15 @@ __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &
         if (cand) {
             int i = __ffs(cand) - 1;
             cand &= cand - 1;
-            test_leaf(s, r, __ldg(s.large_refs + i), T.best, cnt);
+            test_leaf(s, r, __ldg(s.large_refs + i), best, cnt);
         }
     }
-    T.sp = 0;
+}
+
+// point the cursor at the root (T.best already holds the best large-primitive hit)
+__device__ __forceinline__ void trav_start(const DScene &s, Trav &T) {
+    T.stack[0] = RTB_DONE;  // sentinel: popping an empty stack yields "finished"
+    T.sp = 1;
     T.leaf = 0;
     T.cur = s.num_bvh_prims > 0 ? s.root_ref : RTB_DONE;
     if (T.cur < 0) {  // a one-primitive tree: the root is a leaf
@@ -194,28 +208,41 @@ __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &
     }
 }
 
-// Advance the ray through the LBVH: warp-synchronous "while-while" traversal with postponed
-// leaves.  All lanes of `mask` move through the two phases together (the ballots are the
+__device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, unsigned mask, Counters &cnt) {
+    large_prims_best(s, r, T.best, mask, cnt);
+    trav_start(s, T);
+}
+
+// Advance the rays of the warp through the LBVH: warp-synchronous "while-while" traversal with
+// postponed leaves.  All lanes of `mask` move through the two phases together (the ballots are the
 // reconvergence points, so independent thread scheduling cannot let early lanes run ahead into a
 // leaf test on their own):
-//   NODE phase  lanes whose cursor is an internal node take one step per iteration; a lane that
-//               reaches its first leaf postpones it and keeps walking; the phase ends when at most
-//               `node_exit` lanes are still looking for their first leaf;
+//   NODE phase  lanes whose cursor is an internal node take one step per iteration (one 64-byte
+//               fetch, two slab tests, branch-free cursor update); a lane that reaches a leaf
+//               postpones it and keeps walking, and stalls only when it reaches a second one;
 //   LEAF phase  every lane that holds a leaf tests it (the long primitive test is issued once for
 //               all of them).
-// Returns when no lane has work left, or when at least `quota` lanes of the mask have finished
-// their ray (they go and shade / fetch new rays while the others keep their place in the tree;
-// quota <= 0 = run to completion).
-__device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int node_exit,
+// The NODE phase goes on while at least `walk_min` lanes are walking; below that it ends as soon
+// as the other lanes have something better to do: a leaf to test, or -- when `quota` lanes have
+// finished their ray -- new rays to fetch (the call returns; quota <= 0 = run to completion).
+__device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
                                          Counters &cnt) {
     int cur = T.cur, leaf = T.leaf, sp = T.sp;
     Best best = T.best;
-    for (;;) {
+    // every round retires at least one node step or one leaf of some lane; the cap only turns a
+    // logic error into a wrong pixel (caught by the parity tests) instead of a hung GPU
+    for (int round = 0; round < (1 << 22); round++) {
+        unsigned finished;
         for (;;) {
             bool walk = cur >= 0 && cur != RTB_DONE;
-            unsigned searching = __ballot_sync(mask, walk && leaf == 0);
-            if (!searching) break;
-            if (__popc(searching) <= node_exit && __any_sync(mask, leaf < 0)) break;
+            unsigned walking = __ballot_sync(mask, walk);
+            unsigned empty = __ballot_sync(mask, leaf == 0);
+            // invariant: a leaf at the cursor implies a postponed leaf, so !walk && leaf == 0 means done
+            finished = mask & ~walking & empty;
+            if (!walking) break;
+            if (__popc(walking) < walk_min && ((mask & ~empty) || (quota > 0 && __popc(finished) >= quota))) break;
+            RTB_COUNT(cnt, node_iters); RTB_COUNT_N(cnt, node_lanes, __popc(walking)); RTB_COUNT_N(cnt, node_blocked, __popc(mask & ~walking & ~empty));
+            RTB_COUNT_N(cnt, node_done, __popc(finished)); RTB_COUNT_N(cnt, mask_lanes, __popc(mask));
             if (walk) {
                 const float4 *N = s.nodes + 4 * cur;
                 float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
@@ -228,26 +255,27 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                 bool h0 = box_test(lo0, hi0, r, limit, n0);
                 bool h1 = box_test(lo1, hi1, r, limit, n1);
                 int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
-                // branch-free cursor update (selects + one predicated push, one predicated pop):
-                // the four outcomes would otherwise run as four divergent paths
+                // branch-free cursor update (selects, a predicated push, predicated pops): the
+                // four outcomes would otherwise run as four divergent paths
                 bool first0 = h0 && (!h1 || n0 <= n1);
                 int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
-                bool any = h0 || h1;  // invariant on exit: a leaf at the cursor implies a postponed leaf
                 if (h0 && h1 && sp < RTB_STACK) T.stack[sp++] = far;
                 cur = near;
-                if (!any) cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+                // stack[0] holds RTB_DONE as a sentinel (sp >= 1), so a pop is an unconditional load
+                if (!(h0 || h1)) { sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1); }
                 if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
                     leaf = cur;
-                    cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+                    sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
                 }
             }
         }
+        RTB_COUNT(cnt, leaf_iters); RTB_COUNT_N(cnt, leaf_lanes, __popc(__ballot_sync(mask, leaf < 0)));
         if (leaf < 0) {
             test_leaf(s, r, leaf, best, cnt);
             leaf = 0;
             if (cur < 0) {  // a second leaf was reached while the first was pending
                 leaf = cur;
-                cur = sp > 0 ? T.stack[--sp] : RTB_DONE;
+                sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
             }
         }
         unsigned alive = __ballot_sync(mask, cur != RTB_DONE || leaf < 0);
@@ -261,7 +289,7 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
 __device__ __forceinline__ Best trace_bvh(const DScene &s, const Ray &r, unsigned mask, Counters &cnt) {
     Trav T;
     trav_begin(s, r, T, mask, cnt);
-    trav_run(s, r, T, mask, 0, 0, cnt);
+    trav_run(s, r, T, mask, 0, 16, cnt);
     return T.best;
 }
 

@@ -8,7 +8,8 @@
 //
 //   wf_shade     one thread per live pixel: consume the closest hit of the pixel's current ray
 //                (raytracer.cu:74-91), advance the sample / bounce state machine, emit the next
-//                ray, or finish the pixel (raytracer.cu:107-112) and drop it from the queue
+//                ray and test it against the large primitives (walls, floors: a converged loop),
+//                or finish the pixel (raytracer.cu:107-112) and drop it from the queue
 //                (warp-ballot compaction, order preserving inside a warp);
 //   wf_traverse  persistent warps with per-lane dynamic fetch: a lane whose ray is finished
 //                stores the hit and pulls the next ray from the queue (cheap: two float4 loads),
@@ -22,25 +23,33 @@
 //   A {thr.xyz, cur_n}   B {col.xyz, rng bits}   C {acc.xyz, sample << 8 | bounce}
 //   O {origin.xyz, -}    D {direction.xyz, -}    H {t, u, v, code}
 
+#ifndef RTB_TRAV_MIN_BLOCKS
+#define RTB_TRAV_MIN_BLOCKS 8
+#endif
+
 __device__ __forceinline__ void wf_slot_to_pixel(const WfParams &p, int slot, int &x, int &y) {
     int ly = slot / p.width;
     x = slot - ly * p.width;
     y = shard_row(p.shard_rank, p.shard_world, p.band_rows, ly);
 }
 
-template <bool COUNT>
+template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const FrameConsts f = frame_consts(p.rd, p.cam);
     const unsigned int n = p.first ? (unsigned int)(p.width * p.local_rows) : *p.n_in;
     const unsigned int lane = threadIdx.x & 31u;
     unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
+    Counters cnt;
+    cnt = Counters{};
     if (blockIdx.x == 0 && threadIdx.x == 0) *p.fetch = 0;  // for the traversal launch that follows
     // whole warps walk the queue so that the ballot compaction below is converged
     for (unsigned int base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
         unsigned int i = base + lane;
         bool live = i < n;
         int slot = 0;
+        Ray ray;
+        ray.o = f.cam_o; ray.d = v3(0, 0, 1); ray.inv = ray.d;
         if (live) {
             slot = p.queue_in && !p.first ? p.queue_in[i] : (int)i;
             int x, y;
@@ -48,7 +57,6 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
             int array_index = (y * p.width + x) * 3;  // raytracer.cu:123
             V3 pdir = primary_direction(p.cam, x, y);
             Path P;
-            Ray ray;
             if (p.first) {
                 path_begin_pixel(P, array_index, p.time_ms);
                 P.cur_n = 1; P.thr = v3(1, 1, 1); P.col = v3(0, 0, 0);
@@ -83,7 +91,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
                 break;
             }
             if (live) {
-                if (f.aa) apply_antialias(ray, P.rng);
+                if (f.aa) apply_antialias(ray, P.rng);  // change_direction: ray.inv is current again
                 p.st.A[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, P.cur_n);
                 p.st.B[slot] = make_float4(P.col.x, P.col.y, P.col.z, __uint_as_float(P.rng));
                 p.st.C[slot] = make_float4(P.acc.x, P.acc.y, P.acc.z, __uint_as_float(((unsigned int)P.sample << 8) | (unsigned int)P.bounce));
@@ -91,8 +99,20 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
                 p.st.D[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
             }
         }
-        // compaction: the survivors of this warp go to consecutive queue positions, in order
+        // the new rays meet the large primitives here, with the whole warp converged, instead of
+        // at the start of the traversal, where only the few freshly fetched lanes would run it
         unsigned int alive = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            Best first;
+            if (BRUTE) {
+                first.t = RTB_INF_F; first.u = 0; first.v = 0; first.code = -1;
+            } else {
+                if (!f.aa) ray.inv = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);  // ray.cu:198-202
+                large_prims_best(s, ray, first, alive, cnt);
+            }
+            p.st.H[slot] = make_float4(first.t, first.u, first.v, __int_as_float(first.code));
+        }
+        // compaction: the survivors of this warp go to consecutive queue positions, in order
         unsigned int pos = 0;
         if (lane == 0 && alive) pos = atomicAdd(p.n_out, (unsigned int)__popc(alive));
         pos = __shfl_sync(0xffffffffu, pos, 0);
@@ -101,6 +121,9 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
     if (COUNT && p.counters) {
         atomicAdd(p.counters + 0, n_seg);
         atomicAdd(p.counters + 1, n_hit);
+        atomicAdd(p.counters + 2, cnt.box);
+        atomicAdd(p.counters + 3, cnt.tri);
+        atomicAdd(p.counters + 4, cnt.sph);
         atomicAdd(p.counters + 5, n_samples);
     }
 }
@@ -108,14 +131,14 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
 // Persistent traversal: every lane owns one ray at a time; finished lanes store their hit and
 // fetch the next ray as soon as `refill` of them are waiting (or nobody traverses any more).
 template <bool BRUTE, bool COUNT>
-__global__ void __launch_bounds__(RTB_BLOCK_THREADS, 6) wf_traverse_kernel(const WfParams p) {
+__global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_traverse_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const unsigned int FULL = 0xffffffffu;
     const unsigned int n = *p.n_in;
     const unsigned int lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) *p.n_out = 0;  // the counter the next wf_shade appends to
     Counters cnt;
-    cnt.box = cnt.tri = cnt.sph = 0;
+    cnt = Counters{};
     Ray ray;
     ray.o = v3(0, 0, 0); ray.d = v3(0, 0, 1); ray.inv = ray.d;
     Trav T;
@@ -143,18 +166,17 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, 6) wf_traverse_kernel(const
             if (pos + __popc(want) >= n) exhausted = true;
             if (fresh) {
                 slot = p.queue_in ? p.queue_in[mine] : (int)mine;
-                float4 o = p.st.O[slot], d = p.st.D[slot];
+                float4 o = p.st.O[slot], d = p.st.D[slot], h = p.st.H[slot];
                 ray.o = v3(o.x, o.y, o.z);
                 ray.d = v3(d.x, d.y, d.z);
                 ray.inv = v3(1 / d.x, 1 / d.y, 1 / d.z);  // ray.cu:198-202
-            }
-            unsigned int starting = __ballot_sync(FULL, fresh);
-            if (fresh) {
                 if (BRUTE) {
                     T.best = trace_brute(s, ray, cnt);
                     T.cur = RTB_DONE; T.leaf = 0;
                 } else {
-                    trav_begin(s, ray, T, starting, cnt);
+                    // wf_shade left the best large-primitive hit in H: only the tree remains
+                    T.best.t = h.x; T.best.u = h.y; T.best.v = h.z; T.best.code = __float_as_int(h.w);
+                    trav_start(s, T);
                 }
             }
             busy = slot >= 0 && !trav_done(T);
@@ -171,19 +193,30 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, 6) wf_traverse_kernel(const
         if (busy) {
             // while the queue has rays, leave the tree when `refill` lanes are free; afterwards run to the end
             int quota = exhausted ? 0 : p.refill - (32 - __popc(busy_mask));
-            if (!BRUTE) trav_run(s, ray, T, busy_mask, exhausted ? 0 : (quota < 1 ? 1 : quota), p.node_exit, cnt);
+            if (!BRUTE) trav_run(s, ray, T, busy_mask, exhausted ? 0 : (quota < 1 ? 1 : quota), p.walk_min, cnt);
         }
     }
     if (COUNT && p.counters) {
         atomicAdd(p.counters + 2, cnt.box);
         atomicAdd(p.counters + 3, cnt.tri);
         atomicAdd(p.counters + 4, cnt.sph);
+        if (lane == 0) {  // the lane statistics are warp-uniform
+            atomicAdd(p.counters + 8, cnt.node_iters); atomicAdd(p.counters + 9, cnt.node_lanes);
+            atomicAdd(p.counters + 10, cnt.node_blocked); atomicAdd(p.counters + 11, cnt.node_done);
+            atomicAdd(p.counters + 12, cnt.leaf_iters); atomicAdd(p.counters + 13, cnt.leaf_lanes);
+            atomicAdd(p.counters + 14, cnt.mask_lanes);
+        }
     }
 }
 
-cudaError_t launch_wf_shade(const WfParams &p, bool count, int blocks, cudaStream_t st) {
-    if (count) wf_shade_kernel<true><<<blocks, 256, 0, st>>>(p);
-    else wf_shade_kernel<false><<<blocks, 256, 0, st>>>(p);
+cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {
+    if (brute) {
+        if (count) wf_shade_kernel<true, true><<<blocks, 256, 0, st>>>(p);
+        else wf_shade_kernel<true, false><<<blocks, 256, 0, st>>>(p);
+    } else {
+        if (count) wf_shade_kernel<false, true><<<blocks, 256, 0, st>>>(p);
+        else wf_shade_kernel<false, false><<<blocks, 256, 0, st>>>(p);
+    }
     return cudaGetLastError();
 }
 
@@ -199,7 +232,7 @@ cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int bl
 }
 
 cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm) {
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false>, 256, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false, false>, 256, 0);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false>, RTB_BLOCK_THREADS, 0);
 }

@@ -14,6 +14,10 @@ def run(name, sid, p0, p1, W, H, spp, bounces, frames=1, opts=None):
     # counted pass at 1 spp for the op mix
     tr.set_render_data(sc.render_settings(1, bounces)); tr.set_option("counters", 1)
     tr.render_device(1, 7); tr.sync(); c = tr.counters(); tr.set_option("counters", 0)
+    ls = [tr.info(f"lane_stat{k}") for k in range(7)]
+    if ls[0] > 0:
+        info["lanes"] = dict(node_iters_per_ray=ls[0] * 32 / c["segments"], node_walk=ls[1] / ls[0], node_blocked=ls[2] / ls[0], node_done=ls[3] / ls[0],
+                             node_mask=ls[6] / ls[0], leaf_iters_per_ray=ls[4] * 32 / c["segments"], leaf_lanes=ls[5] / max(1, ls[4]))
     tr.set_render_data(sc.render_settings(spp, bounces)); tr.reset()
     tr.render_device(1, 1); tr.sync()  # warm-up
     tr.reset(); tr.render_device(frames, 100); tr.sync(); ms = tr.device_ms()
@@ -25,51 +29,60 @@ def run(name, sid, p0, p1, W, H, spp, bounces, frames=1, opts=None):
     tr.close()
 
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "sweep":
-        for r in (1, 4, 8, 12, 16, 20, 24, 28, 32):
-            run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"refill": r})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 8})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 16})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": 32})
+    C3 = ("C3", 0, 0, 0, 1920, 1080, 32, 8)
+    which = sys.argv[1] if len(sys.argv) > 1 else ""
+    if which == "quick":
+        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 8, "walk_min": 16})
+        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 8, "walk_min": 20})
+        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 4, "walk_min": 16})
+        run(*C3, opts={"kernel": 0, "builder": 1, "walk_min": 12})
+        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1, "builder": 0, "walk_min": 16})
         sys.exit(0)
-    if len(sys.argv) > 1 and sys.argv[1] == "sweep4":
-        C3 = ("C3", 0, 0, 0, 1920, 1080, 32, 8)
-        run(*C3, opts={"kernel": 0})
-        run(*C3, opts={"kernel": 1})
-        for b, ls, rad in ((1, 1, 16), (1, 0, 16), (1, 0, 8), (1, 0, 32), (0, 0, 16)):
-            for kern in (0, 1):
-                run(*C3, opts={"kernel": kern, "builder": b, "large_split": ls, "ploc_radius": rad})
+    if which == "lanes2":
+        for wm in (8, 12, 16, 20, 24, 28):
+            run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 8, "walk_min": wm})
         for r in (2, 4, 16):
-            run(*C3, opts={"kernel": 1, "builder": 1, "large_split": 0, "wf_refill": r})
-        for ne in (0, 2, 8):
-            run(*C3, opts={"kernel": 1, "builder": 1, "large_split": 0, "node_exit": ne})
+            run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": r, "walk_min": 20})
+        for wm in (12, 20, 28):
+            run(*C3, opts={"kernel": 0, "builder": 1, "walk_min": wm})
+        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1, "builder": 0, "walk_min": 20})
+        sys.exit(0)
+    if which == "lanes":
+        for r in (8, 16, 24):
+            run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": r})
+        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 16, "node_exit": 0})
+        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 16, "node_exit": 8})
+        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1, "builder": 0})
+        sys.exit(0)
+    if which == "sweep6":
+        for r in (4, 8, 16):
+            for ne in (0, 4):
+                run(*C3, opts={"kernel": 1, "wf_refill": r, "node_exit": ne})
+        run(*C3, opts={"kernel": 0})
+        for b, ls in ((1, 1), (1, 0)):
+            run(*C3, opts={"kernel": 1, "builder": b, "large_split": ls})
+        for bps in (4, 6):
+            run(*C3, opts={"kernel": 1, "blocks_per_sm": bps})
         for kern in (0, 1):
-            for b, ls in ((0, 1), (1, 0)):
-                run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern, "builder": b, "large_split": ls})
-                run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern, "builder": b, "large_split": ls})
-                run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern, "builder": b, "large_split": ls})
+            run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern})
+            run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern})
+            run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern})
         sys.exit(0)
-    if len(sys.argv) > 1 and sys.argv[1] == "sweep3":
-        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 0})
-        for r in (2, 4, 8, 16, 32):
-            for ne in (0, 4):
-                run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": r, "node_exit": ne})
-        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": 8, "node_exit": 4, "blocks_per_sm": 4})
-        run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"kernel": 1, "wf_refill": 8, "node_exit": 4, "blocks_per_sm": 6})
-        run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": 0})
-        run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": 1})
-        run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": 0})
-        run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": 1})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 0})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1})
-        sys.exit(0)
-    if len(sys.argv) > 1 and sys.argv[1] == "sweep2":
-        for r in (4, 8, 12, 16, 24):
-            for ne in (0, 2, 4, 8):
-                run("C3", 0, 0, 0, 1920, 1080, 32, 8, opts={"refill": r, "node_exit": ne})
-        for r in (8, 16):
-            for ne in (0, 4):
-                run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"refill": r, "node_exit": ne})
+    if which == "sweep5":
+        for kern in (0, 1):
+            for lm in (4, 8, 12, 16, 20, 24):
+                run(*C3, opts={"kernel": kern, "leaf_min": lm})
+        for r in (1, 2, 4, 8, 16):
+            run(*C3, opts={"kernel": 1, "wf_refill": r})
+        for r in (4, 8, 16, 24):
+            run(*C3, opts={"kernel": 0, "refill": r})
+        for kern in (0, 1):
+            for b, ls in ((1, 1), (1, 0), (0, 0)):
+                run(*C3, opts={"kernel": kern, "builder": b, "large_split": ls})
+        for kern in (0, 1):
+            run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern})
+            run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern})
+            run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern})
         sys.exit(0)
     run("C1", 0, 0, 0, 1000, 800, 100, 5)
     run("C2", 5, 0, 0, 1920, 1080, 64, 8)

@@ -50,6 +50,31 @@ def test_ids_and_radiance_vs_reference_cuda(sid, p0, p1):
 
 
 @needs_ref
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_converged_radiance_vs_reference_cuda(kernel):
+    """north_star acceptance: converged radiance within RMSE < 1e-3 (PSNR > 45 dB) of the reference
+    render at matched spp -- default build of both sides, glass scene and monkey scene, 128 spp,
+    megakernel and wavefront."""
+    for sid in (3, 0):
+        spp, bounces = 128, 5
+        ref = ob.RefCuda(W, H)
+        ref.init(sid, 0, 0, spp, bounces, True)
+        r_img = np.zeros((H, W, 3), np.float32)
+        ref.render_kernel(r_img, 0, 2024)
+        scene = rtb.Scene(sid, 0, 0)
+        tr = rtb.Tracer(0)
+        tr.set_option("kernel", kernel)
+        tr.setup(scene, W, H, spp, bounces)
+        img = np.zeros((H, W, 3), np.float32)
+        tr.render(img, 0, 2024)
+        tr.close()
+        rmse = float(np.sqrt(((img - r_img) ** 2).mean()))
+        psnr = 20 * np.log10(max(1.0, float(r_img.max())) / max(rmse, 1e-12))
+        print(f"scene {sid} kernel {kernel} at {spp} spp: RMSE {rmse:.3e}, PSNR {psnr:.1f} dB, bit-identical {float((img == r_img).mean()):.4f}")
+        assert rmse < 1e-3 and psnr > 45
+
+
+@needs_ref
 def test_reference_render_entry_point_matches_its_kernel():
     """render() (src/dispatch.cu:156) and the harness launch of the same kernel agree bit for bit."""
     ref = ob.RefCuda(W, H)
