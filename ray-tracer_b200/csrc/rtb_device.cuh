@@ -43,11 +43,13 @@ struct DScene {
     int num_prims;       // all primitives (leaves of the LBVH + large primitives)
     int num_bvh_prims;   // leaves of the LBVH
     int root_ref;        // encoded like a child ref (a 1-primitive tree has a leaf root)
+    float4 root_node[4]; // copy of the root node: lives in the kernel parameters (uniform loads)
     // Large primitives (walls, floors: boxes that span a big share of the scene) are kept out of
     // the tree and tested first, in a warp-uniform loop; their hits bound the tree traversal.
     const int *large_refs;
     const float4 *large_boxes;  // 2 float4 per large primitive: padded lo, hi
     int num_large;
+    unsigned int large_sphere_mask;  // bit i: large primitive i is a sphere
     // triangles, 3 float4 each: {p0.xyz, s1.x} {s1.yz, s2.xy} {s2.z, n.xyz}.  KIND_TRI leaves
     // name one triangle, KIND_QUAD* leaves the first of two consecutive ones (t1, t2 of a Quad).
     const float4 *tris;

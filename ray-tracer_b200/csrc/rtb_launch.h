@@ -44,12 +44,16 @@ struct WfParams {
     const float *prev;
     float *out;
     int shard_rank, shard_world, band_rows, local_rows;
+    int slot_base, slot_count;  // the row group this launch works on: slots [slot_base, slot_base + slot_count)
     WfState st;
+    unsigned char *alive;       // per slot: 1 while the pixel still has samples to trace
     const int *queue_in;        // live pixel slots of this iteration (nullptr = identity 0..n-1)
     int *queue_out;             // live slots of the next iteration
     const unsigned int *n_in;   // device counters
     unsigned int *n_out;        // wf_shade: appended to; wf_traverse: zeroed for the next wf_shade
     unsigned int *fetch;        // wf_traverse: next queue position to hand out (zeroed by wf_shade)
+    int *tqueue;                // slots whose ray has to enter the tree (written by wf_shade, read by wf_traverse)
+    unsigned int *tn, *tn_next; // its length (wf_shade appends, wf_traverse reads) / the counter wf_traverse zeroes for the next wf_shade
     int first;                  // wf_shade: 1 = no hit to consume yet (start of the frame)
     int refill, walk_min;
     unsigned long long *counters;
@@ -67,6 +71,7 @@ struct LaunchConfig {
     cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);                     \
     cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
     cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \
+    cudaError_t launch_wf_rebuild(int slot_base, int n_slots, const unsigned char *alive, int *block_count, int *queue, unsigned int *total, cudaStream_t st); \
     }
 RTB_DECLARE_VARIANT(fast)
 RTB_DECLARE_VARIANT(strict)

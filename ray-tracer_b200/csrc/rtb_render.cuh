@@ -72,6 +72,15 @@ __device__ __forceinline__ void apply_antialias(Ray &r, uint32_t &rng) {
     change_direction(r, normalised(r.d + off));
 }
 
+// The reference recomputes direction_inv at every change of direction (ray.cu:198-202), but only
+// the box tests read it, and only for the ray as it enters get_ray_collision: scatter and
+// sample start set the direction alone and the inverse is taken once, here, after the antialias
+// jitter (which is itself a change_direction when enabled).  Same IEEE divides, same values.
+__device__ __forceinline__ void ray_finalise(Ray &r, bool aa, uint32_t &rng) {
+    if (aa) apply_antialias(r, rng);
+    else change_direction(r, r.d);
+}
+
 // Ray::reflect, ray.cu:67-75 with diffuse_reflect :157-170, true_lambertian_reflect :172-178,
 // perfect_reflect :180-186, lerp :32-34
 __device__ __forceinline__ void reflect(Ray &r, const Surface &sf, float smoothness, uint32_t &rng) {
@@ -85,7 +94,7 @@ __device__ __forceinline__ void reflect(Ray &r, const Surface &sf, float smoothn
     float dn = dot(r.d, sf.normal);
     V3 spec = normalised(r.d - sf.normal * 2.f * dn);
     r.o = sf.point;
-    change_direction(r, normalised(diffuse + (spec - diffuse) * smoothness));
+    r.d = normalised(diffuse + (spec - diffuse) * smoothness);  // direction_inv: see ray_finalise
 }
 
 // Ray::refract, ray.cu:77-128 + get_reflection_coeff :188-196
@@ -114,7 +123,7 @@ static __device__ __noinline__ void refract(Ray &r, const Surface &sf, float mat
     else perp = v3(0, 0, 0);
     V3 res = refn * cos(theta2) + perp * sin(theta2);
     r.o = sf.point;
-    change_direction(r, normalised(res));
+    r.d = normalised(res);  // direction_inv: see ray_finalise
 }
 
 // Texture::get_texture_colour, material.cu:53-124
@@ -233,7 +242,7 @@ __device__ __forceinline__ void path_write_pixel(const Path &P, int spp, int fra
 // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
 __device__ __forceinline__ void path_begin_sample(const FrameConsts &f, V3 pdir, Ray &ray, Path &P) {
     ray.o = f.cam_o;
-    change_direction(ray, pdir);
+    ray.d = pdir;  // direction_inv: see ray_finalise
     P.cur_n = 1;
     P.thr = v3(1, 1, 1);
     P.col = v3(0, 0, 0);
@@ -325,7 +334,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
                     break;  // a ray is ready
                 }
                 if (mode != IDLE) {
-                    if (f.aa) apply_antialias(ray, P.rng);
+                    ray_finalise(ray, f.aa, P.rng);
                     fresh = true;
                     mode = TRAVERSING;
                 }

@@ -187,12 +187,51 @@ __device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, 
         RTB_COUNT(cnt, box);
         if (box_test(__ldg(s.large_boxes + 2 * i), __ldg(s.large_boxes + 2 * i + 1), r, RTB_INF_F, tn)) cand |= 1u << i;
     }
-    while (__any_sync(mask, cand != 0)) {
-        if (cand) {
-            int i = __ffs(cand) - 1;
-            cand &= cand - 1;
-            test_leaf(s, r, __ldg(s.large_refs + i), best, cnt);
+    // triangles / quads first, then spheres: inside one loop every lane runs the same kind of test
+    unsigned part = cand & ~s.large_sphere_mask;
+    cand &= s.large_sphere_mask;
+    for (int pass = 0; pass < 2; pass++) {
+        while (__any_sync(mask, part != 0)) {
+            if (part) {
+                int i = __ffs(part) - 1;
+                part &= part - 1;
+                test_leaf(s, r, __ldg(s.large_refs + i), best, cnt);
+            }
         }
+        part = cand;
+    }
+}
+
+// The root's node step, taken with the node in the kernel parameters (uniform loads, no L1
+// traffic) by the kernel that creates the ray, where the whole warp is converged.  Returns the
+// child to start at (`first`; RTB_DONE = the ray cannot touch the tree closer than `best`) and the
+// child to visit afterwards (`second`, 0 = none).
+__device__ __forceinline__ void root_step(const DScene &s, const Ray &r, const Best &best, int &first, int &second, Counters &cnt) {
+    first = RTB_DONE; second = 0;
+    if (s.num_bvh_prims <= 0) return;
+    if (s.root_ref < 0) { first = s.root_ref; return; }  // a one-primitive tree: the root is a leaf
+    float limit = best.t * 1.0001f, n0, n1;
+    RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
+    bool h0 = box_test(s.root_node[0], s.root_node[1], r, limit, n0);
+    bool h1 = box_test(s.root_node[2], s.root_node[3], r, limit, n1);
+    int r0 = __float_as_int(s.root_node[0].w), r1 = __float_as_int(s.root_node[2].w);
+    bool first0 = h0 && (!h1 || n0 <= n1);
+    if (h0 || h1) first = first0 ? r0 : r1;
+    if (h0 && h1) second = first0 ? r1 : r0;
+}
+
+// enter the tree below the root with the outcome of root_step
+__device__ __forceinline__ void trav_start_below_root(Trav &T, int first, int second) {
+    T.stack[0] = RTB_DONE;  // sentinel: popping an empty stack yields "finished"
+    T.sp = 1;
+    if (second != 0) T.stack[T.sp++] = second;
+    T.leaf = 0;
+    T.cur = first;
+    if (T.cur < 0) {  // a leaf: postpone it, go on with the other child
+        T.leaf = T.cur;
+        T.sp--;
+        T.cur = T.stack[T.sp];
+        T.sp = max(T.sp, 1);
     }
 }
 

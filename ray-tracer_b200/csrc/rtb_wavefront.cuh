@@ -21,8 +21,11 @@
 //
 // Per-pixel record (6 float4 = 96 B, SoA by field, indexed by the pixel's local slot):
 //   A {thr.xyz, cur_n}   B {col.xyz, rng bits}   C {acc.xyz, sample << 8 | bounce}
-//   O {origin.xyz, -}    D {direction.xyz, -}    H {t, u, v, code}
+//   O {origin.xyz, first node below the root}   D {direction.xyz, second node}   H {t, u, v, code}
 
+#ifndef RTB_SHADE_MIN_BLOCKS
+#define RTB_SHADE_MIN_BLOCKS 4
+#endif
 #ifndef RTB_TRAV_MIN_BLOCKS
 #define RTB_TRAV_MIN_BLOCKS 8
 #endif
@@ -34,10 +37,10 @@ __device__ __forceinline__ void wf_slot_to_pixel(const WfParams &p, int slot, in
 }
 
 template <bool BRUTE, bool COUNT>
-__global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
+__global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const FrameConsts f = frame_consts(p.rd, p.cam);
-    const unsigned int n = p.first ? (unsigned int)(p.width * p.local_rows) : *p.n_in;
+    const unsigned int n = p.first ? (unsigned int)p.slot_count : *p.n_in;
     const unsigned int lane = threadIdx.x & 31u;
     unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
     Counters cnt;
@@ -51,13 +54,14 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
         Ray ray;
         ray.o = f.cam_o; ray.d = v3(0, 0, 1); ray.inv = ray.d;
         if (live) {
-            slot = p.queue_in && !p.first ? p.queue_in[i] : (int)i;
+            slot = p.first ? p.slot_base + (int)i : p.queue_in[i];
             int x, y;
             wf_slot_to_pixel(p, slot, x, y);
             int array_index = (y * p.width + x) * 3;  // raytracer.cu:123
             V3 pdir = primary_direction(p.cam, x, y);
             Path P;
             if (p.first) {
+                p.alive[slot] = 1;
                 path_begin_pixel(P, array_index, p.time_ms);
                 P.cur_n = 1; P.thr = v3(1, 1, 1); P.col = v3(0, 0, 0);
                 ray.o = f.cam_o; ray.d = pdir; ray.inv = pdir;
@@ -82,6 +86,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
                     if (P.sample >= f.spp) {
                         path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
                         live = false;
+                        p.alive[slot] = 0;
                         break;
                     }
                     path_begin_sample(f, pdir, ray, P);
@@ -91,27 +96,38 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const WfParams p) {
                 break;
             }
             if (live) {
-                if (f.aa) apply_antialias(ray, P.rng);  // change_direction: ray.inv is current again
+                ray_finalise(ray, f.aa, P.rng);  // antialias jitter, direction_inv
                 p.st.A[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, P.cur_n);
                 p.st.B[slot] = make_float4(P.col.x, P.col.y, P.col.z, __uint_as_float(P.rng));
                 p.st.C[slot] = make_float4(P.acc.x, P.acc.y, P.acc.z, __uint_as_float(((unsigned int)P.sample << 8) | (unsigned int)P.bounce));
-                p.st.O[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.f);
-                p.st.D[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
             }
         }
         // the new rays meet the large primitives here, with the whole warp converged, instead of
         // at the start of the traversal, where only the few freshly fetched lanes would run it
+        // ... and take the root's node step (the root node sits in the kernel parameters): a ray
+        // that cannot touch the tree closer than its large-primitive hit never enters wf_traverse
         unsigned int alive = __ballot_sync(0xffffffffu, live);
+        bool enter = false;
         if (live) {
             Best first;
+            int start = RTB_DONE, then = 0;
             if (BRUTE) {
                 first.t = RTB_INF_F; first.u = 0; first.v = 0; first.code = -1;
+                enter = true;
             } else {
-                if (!f.aa) ray.inv = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);  // ray.cu:198-202
                 large_prims_best(s, ray, first, alive, cnt);
+                root_step(s, ray, first, start, then, cnt);
+                enter = start != RTB_DONE;
             }
+            p.st.O[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __int_as_float(start));
+            p.st.D[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __int_as_float(then));
             p.st.H[slot] = make_float4(first.t, first.u, first.v, __int_as_float(first.code));
         }
+        unsigned int entering = __ballot_sync(0xffffffffu, enter);
+        unsigned int tpos = 0;
+        if (lane == 0 && entering) tpos = atomicAdd(p.tn, (unsigned int)__popc(entering));
+        tpos = __shfl_sync(0xffffffffu, tpos, 0);
+        if (enter) p.tqueue[tpos + __popc(entering & ((1u << lane) - 1u))] = slot;
         // compaction: the survivors of this warp go to consecutive queue positions, in order
         unsigned int pos = 0;
         if (lane == 0 && alive) pos = atomicAdd(p.n_out, (unsigned int)__popc(alive));
@@ -134,9 +150,12 @@ template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_traverse_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const unsigned int FULL = 0xffffffffu;
-    const unsigned int n = *p.n_in;
+    const unsigned int n = *p.tn;
     const unsigned int lane = threadIdx.x & 31u;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *p.n_out = 0;  // the counter the next wf_shade appends to
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // the counters the next wf_shade appends to
+        *p.n_out = 0;
+        *p.tn_next = 0;
+    }
     Counters cnt;
     cnt = Counters{};
     Ray ray;
@@ -165,7 +184,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
             bool fresh = slot < 0 && mine < n;
             if (pos + __popc(want) >= n) exhausted = true;
             if (fresh) {
-                slot = p.queue_in ? p.queue_in[mine] : (int)mine;
+                slot = p.tqueue[mine];
                 float4 o = p.st.O[slot], d = p.st.D[slot], h = p.st.H[slot];
                 ray.o = v3(o.x, o.y, o.z);
                 ray.d = v3(d.x, d.y, d.z);
@@ -176,7 +195,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
                 } else {
                     // wf_shade left the best large-primitive hit in H: only the tree remains
                     T.best.t = h.x; T.best.u = h.y; T.best.v = h.z; T.best.code = __float_as_int(h.w);
-                    trav_start(s, T);
+                    trav_start_below_root(T, __float_as_int(o.w), __float_as_int(d.w));
                 }
             }
             busy = slot >= 0 && !trav_done(T);
@@ -207,6 +226,66 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
             atomicAdd(p.counters + 14, cnt.mask_lanes);
         }
     }
+}
+
+// ---- queue rebuild -----------------------------------------------------------------------------
+// The ballot compaction in wf_shade keeps the order inside a warp but appends the warps in arrival
+// order, so while pixels keep finishing the queue slowly turns into short runs of neighbouring
+// slots in random order, and the per-slot records are no longer read in whole sectors.  Every few
+// iterations the queue is rebuilt in slot order from the per-slot alive flags: block counts, a
+// one-block scan, an order-preserving scatter.
+constexpr int WF_QT = 256;
+
+__global__ void wf_queue_count_kernel(int base, int n, const unsigned char *alive, int *block_count) {
+    int i = blockIdx.x * WF_QT + threadIdx.x;
+    int c = __syncthreads_count(i < n && alive[base + i]);
+    if (threadIdx.x == 0) block_count[blockIdx.x] = c;
+}
+
+__global__ void wf_queue_scan_kernel(int num_blocks, int *block_count, unsigned int *total) {
+    __shared__ int part[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < num_blocks; base += 1024) {
+        int i = base + threadIdx.x;
+        int v = i < num_blocks ? block_count[i] : 0;
+        part[threadIdx.x] = v;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            int t = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+            __syncthreads();
+            part[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < num_blocks) block_count[i] = carry + part[threadIdx.x] - v;  // exclusive
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += part[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = (unsigned int)carry;
+}
+
+__global__ void wf_queue_scatter_kernel(int base, int n, const unsigned char *alive, const int *block_offset, int *queue) {
+    __shared__ int warp_sum[WF_QT / 32];
+    int i = blockIdx.x * WF_QT + threadIdx.x;
+    bool k = i < n && alive[base + i];
+    unsigned int b = __ballot_sync(0xffffffffu, k);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warp_sum[warp] = __popc(b);
+    __syncthreads();
+    int off = block_offset[blockIdx.x];
+    for (int w = 0; w < warp; w++) off += warp_sum[w];
+    off += __popc(b & ((1u << lane) - 1u));
+    if (k) queue[off] = base + i;
+}
+
+cudaError_t launch_wf_rebuild(int slot_base, int n_slots, const unsigned char *alive, int *block_count, int *queue, unsigned int *total, cudaStream_t st) {
+    int blocks = (n_slots + WF_QT - 1) / WF_QT;
+    wf_queue_count_kernel<<<blocks, WF_QT, 0, st>>>(slot_base, n_slots, alive, block_count);
+    wf_queue_scan_kernel<<<1, 1024, 0, st>>>(blocks, block_count, total);
+    wf_queue_scatter_kernel<<<blocks, WF_QT, 0, st>>>(slot_base, n_slots, alive, block_count, queue);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {

@@ -21,6 +21,9 @@ def run(name, sid, p0, p1, W, H, spp, bounces, frames=1, opts=None):
     tr.set_render_data(sc.render_settings(spp, bounces)); tr.reset()
     tr.render_device(1, 1); tr.sync()  # warm-up
     tr.reset(); tr.render_device(frames, 100); tr.sync(); ms = tr.device_ms()
+    if int(tr.info("kernel")) == 1:
+        tr.set_option("wf_timing", 1); tr.reset(); tr.render_device(1, 100); tr.sync(); tr.set_option("wf_timing", 0)
+        info["wf_ms"] = dict(shade=tr.info("wf_shade_ms"), traverse=tr.info("wf_traverse_ms"), total=tr.info("wf_total_ms"))
     seg_per_sample = c["segments"] / c["samples"]
     rays = seg_per_sample * W * H * spp * frames
     out = dict(name=name, opts=opts, ms=ms, mrays_s=rays / ms / 1e3, spp_s=spp * frames / (ms / 1e3), seg_per_sample=seg_per_sample,
@@ -31,6 +34,25 @@ def run(name, sid, p0, p1, W, H, spp, bounces, frames=1, opts=None):
 if __name__ == "__main__":
     C3 = ("C3", 0, 0, 0, 1920, 1080, 32, 8)
     which = sys.argv[1] if len(sys.argv) > 1 else ""
+    if which == "groups":
+        for g, st in ((1, 1), (2, 1), (2, 2), (4, 1), (4, 2), (8, 2), (16, 2)):
+            run("C3-256", 0, 0, 0, 1920, 1080, 256, 8, opts={"wf_groups": g, "wf_streams": st})
+        sys.exit(0)
+    if which == "rebuild":
+        for rb in (0, 4, 16, 64):
+            run("C3-256", 0, 0, 0, 1920, 1080, 256, 8, opts={"wf_rebuild": rb})
+        run(*C3, opts={"wf_rebuild": 0})
+        run(*C3, opts={"wf_rebuild": 16})
+        sys.exit(0)
+    if which == "one":
+        run(*C3, opts={})
+        sys.exit(0)
+    if which == "split":
+        run(*C3, opts={})
+        run("C3-256", 0, 0, 0, 1920, 1080, 256, 8, opts={})
+        run("C1", 0, 0, 0, 1000, 800, 100, 5, opts={})
+        run("C2", 5, 0, 0, 1920, 1080, 64, 8, opts={})
+        sys.exit(0)
     if which == "quick":
         run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 8, "walk_min": 16})
         run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 8, "walk_min": 20})

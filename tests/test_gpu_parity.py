@@ -131,6 +131,34 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
         assert out[0][2][k] == out[1][2][k]
 
 
+@pytest.mark.parametrize("groups,streams", [(2, 1), (3, 2), (7, 2)])
+def test_wavefront_row_groups_and_streams(tracer, groups, streams):
+    """Row groups (L2 residency) and two concurrent streams only reorder the work: same bits."""
+    scene = _scene(0, 0, 0)
+    Ws, Hs = 203, 151
+    tracer.setup(scene, Ws, Hs, 3, 4)
+    ref = np.zeros((Hs, Ws, 3), np.float32)
+    f = tracer.render(ref, 0, 99)
+    f = tracer.render(ref, f, 100)
+    try:
+        tracer.set_option("wf_groups", groups)
+        tracer.set_option("wf_streams", streams)
+        tracer.set_option("wf_rebuild", 2)
+        img = np.zeros((Hs, Ws, 3), np.float32)
+        f = tracer.render(img, 0, 99)
+        f = tracer.render(img, f, 100)
+        assert (img == ref).all()
+        tracer.reset()
+        tracer.render_device(2, 99, 1)
+        tracer.sync()
+        dev, fr = tracer.download()
+        assert fr == 2 and (dev == ref).all()
+    finally:
+        tracer.set_option("wf_groups", 1)
+        tracer.set_option("wf_streams", 1)
+        tracer.set_option("wf_rebuild", 16)
+
+
 def test_wavefront_sharded_and_odd_sizes(tracer):
     scene = _scene(3, 0, 0)
     Ws, Hs = 203, 151
