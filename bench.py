@@ -13,8 +13,15 @@ value  = Mrays/s, device-timed (CUDA events on the render stream), scene and acc
          resident in HBM; whole job (all ranks), time = max over ranks.
 e2e    = the same metric through the reference-facing entry point rtb_render() == render(
          VariableRenderData*, int): host image in, host image out, H2D and D2H inside the timed region.
-N > 1  : one process per GPU (torchrun), row-cyclic band sharding of the SAME frame (strong scaling,
-         image identical to 1 GPU), NCCL all-gather of the bands inside the timed region.
+N > 1  : one process per GPU (torchrun).  Two partitionings, --sharding:
+         tiles   row-cyclic bands of the SAME frame (strong scaling, image bit-identical to 1 GPU),
+                 NCCL all-gather of the bands inside the timed region;
+         slices  sample slices of a progressive render: every rank renders the whole frame for its
+                 own frames (current_time_ms = base + rank), NCCL all-reduce of the accumulation
+                 buffer inside the timed region; a step yields N x spp samples (weak scaling).
+         auto    (default) tiles for the 4K configs (C4: BASELINE.json's tile-sharded config), slices
+                 otherwise: a 1080p frame cut in 8 leaves 0.26 M pixels per GPU, too few rays per
+                 launch to fill 148 SMs (measured at N = 2 on C3: tiles 83 % efficient).
 --impl reference : the reference's OWN CUDA build (baseline/_ref, unmodified sources, resolution
          constants patched) on the same workload at a bounded spp per step (a rate, spp independent);
          if that library is absent, the reference source on the host cores (oracle/_ref), else the C port.
@@ -230,6 +237,7 @@ def main():
     ap.add_argument("--impl", default="rtb")
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--band-rows", type=int, default=8)
+    ap.add_argument("--sharding", default="auto", choices=["auto", "tiles", "slices"])
     ap.add_argument("--ref-spp", type=int, default=8, help="spp per step of the reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront (library default)")
@@ -258,6 +266,12 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     sid, p0, p1, W, H, spp, bounces = WORKLOADS[args.workload]
+    sharding = args.sharding
+    if sharding == "auto":
+        sharding = "tiles" if W * H >= 3840 * 2160 else "slices"
+    if world == 1:
+        sharding = "none"
+    tiles, slices = sharding == "tiles", sharding == "slices"
     scene = rtb.Scene(sid, p0, p1)
     tr = rtb.Tracer(local_rank)
     if args.kernel is not None:
@@ -267,7 +281,7 @@ def main():
     tr.setup(scene, W, H, spp, bounces)
     kernel_kind = int(tr.info("kernel"))
     per_frame = int(tr.info("launches_per_frame"))
-    if world > 1:
+    if tiles:
         tr.set_shard(rank, world, args.band_rows)
     ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
     rows_mine, rows_pad = tr.shard_rows()
@@ -278,27 +292,41 @@ def main():
         torch.cuda.synchronize()
 
     with torch.cuda.stream(ext):
-        dense = gathered = None
-        if world > 1:
+        dense = gathered = accum = None
+        if tiles:
             dense = torch.zeros(rows_pad * W * 3, device="cuda", dtype=torch.float32)
             gathered = torch.empty(world * rows_pad * W * 3, device="cuda", dtype=torch.float32)
+        if slices:
+            class _Dev:  # the library's accumulation image as a torch tensor (no copy)
+                __cuda_array_interface__ = {"shape": (H * W * 3,), "typestr": "<f4", "data": (tr.device_image_ptr(), False), "version": 2}
+            accum = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
 
-        def device_step(k):
-            """one frame, everything resident: render my bands (+ pack, all-gather, unpack)"""
-            tr.reset()
-            tr.render_device(1, 1000 + k)
-            n = 1
-            if world > 1:
+        def exchange():
+            """the one exchange step of a frame; returns the kernels it launched"""
+            if tiles:
                 tr.shard_pack(dense.data_ptr())
                 dist.all_gather_into_tensor(gathered, dense)
                 tr.shard_unpack(gathered.data_ptr())
-                n += 2
-            return n
+                return 2
+            if slices:
+                dist.all_reduce(accum)      # sum of the ranks' running means ...
+                accum.mul_(1.0 / world)     # ... -> mean over world x spp samples
+                return 1
+            return 0
+
+        def frame_time(k):
+            return 1000 + k * (world if slices else 1) + (rank if slices else 0)
+
+        def device_step(k):
+            """one step, everything resident: render my share, then the exchange"""
+            tr.reset()
+            tr.render_device(1, frame_time(k))
+            return per_frame + exchange()
 
         # op mix / ray count of one step: counter build, same inputs, untimed
         tr.set_option("counters", 1)
         tr.reset()
-        tr.render_device(1, 1000)
+        tr.render_device(1, frame_time(0))
         tr.sync()
         cnt = tr.counters()
         tr.set_option("counters", 0)
@@ -322,14 +350,9 @@ def main():
         for k in range(args.steps):
             kev[k][0].record(ext)
             tr.reset()
-            tr.render_device(1, 1000 + k)
+            tr.render_device(1, frame_time(k))
             kev[k][1].record(ext)
-            launches += per_frame
-            if world > 1:
-                tr.shard_pack(dense.data_ptr())
-                dist.all_gather_into_tensor(gathered, dense)
-                tr.shard_unpack(gathered.data_ptr())
-                launches += 2
+            launches += per_frame + exchange()
         ev1.record(ext)
         barrier()
         clocks = sampler.stop() if rank == 0 else None
@@ -350,11 +373,10 @@ def main():
                 himg[:] = 0  # the caller's previous_render (frame 0)
                 tr.render(himg, 0, 1000 + k)  # H2D + kernel + D2H + sync
             else:
+                himg[:] = 0
                 tr.set_accumulation(himg, 0)  # H2D
-                tr.render_device(1, 1000 + k)
-                tr.shard_pack(dense.data_ptr())
-                dist.all_gather_into_tensor(gathered, dense)
-                tr.shard_unpack(gathered.data_ptr())
+                tr.render_device(1, frame_time(k))
+                exchange()
                 out, _ = tr.download()  # D2H + sync
                 himg[:] = out.reshape(-1)
 
@@ -379,18 +401,19 @@ def main():
         fpr = flops_per_ray(cnt)
         peaks = load_peaks()
         nominal_peak = 148 * 128 * 2 * (peaks["sm_max_mhz"] if peaks else 1965.0) * 1e6 / 1e12
-        kernel_rate = rays_per_step / world / kernel_ms / 1e3      # Mrays/s of ONE launch on one GPU
+        kernel_rate = rays_per_step / world / kernel_ms / 1e3      # Mrays/s of one GPU's render kernels
         achieved_tf = kernel_rate * 1e6 * fpr / 1e12
         hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
         achieved_gbs = (kernel_rate * 1e6 * bytes_per_ray(cnt) + (W * H // world) * 24 / (kernel_ms / 1e3)) / 1e9
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if slices else "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "spp_per_s_1080p": (spp / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
+            "spp_per_s_1080p": (spp * (world if slices else 1) / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
             "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "scene_id": sid, "width": W, "height": H, "spp_per_step": spp,
                        "bounces": bounces, "rays_per_step": rays_per_step, "segments_per_sample": cnt["segments"] / max(1, cnt["samples"]),
-                       "sharding": "none" if world == 1 else f"row-cyclic bands of {args.band_rows} rows, NCCL all-gather per frame",
+                       "sharding": "none" if world == 1 else (f"tiles: row-cyclic bands of {args.band_rows} rows of one frame, NCCL all-gather per frame" if tiles else
+                                                                f"sample slices: {world} frames of {spp} spp per step (one per rank, own time seed), NCCL all-reduce of the accumulation buffer per step"),
                        "kernel": ("wavefront: wf_shade + persistent wf_traverse per path segment" if kernel_kind == 1 else "persistent megakernel")
                                  + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
                        "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
