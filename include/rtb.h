@@ -173,6 +173,13 @@ int rtb_sync(rtb_ctx *ctx);
 int rtb_reset_accumulation(rtb_ctx *ctx);                                   /* frame counter = 0, image = 0 */
 int rtb_set_accumulation(rtb_ctx *ctx, const float *rgb_host, int frame_num); /* resume (checkpoint) */
 int rtb_download(rtb_ctx *ctx, float *rgb_host, int *frame_num_out);
+/* Display conversion of the accumulation image: == parse_pixel_colours,
+ * src/main.cu:343-371 (colour = (int)(value * 255) clamped to [0, 255], alpha 255), as one kernel on
+ * the device; rgba_host receives width*height*4 bytes.  No window: the bytes are what the reference
+ * hands to sf::Texture::update (src/main.cu:380). */
+int rtb_display_rgba8(rtb_ctx *ctx, uint8_t *rgba_host);
+/* the same bytes without alpha as a binary PPM (P6) file: the headless stand-in for the window */
+int rtb_write_ppm(rtb_ctx *ctx, const char *path);
 /* device address of the accumulation image (width*height*3 floats) and the context's cudaStream_t,
  * for callers that run collectives on it (torch.distributed / NCCL) */
 void *rtb_device_image(rtb_ctx *ctx);

@@ -692,3 +692,20 @@ void pto_default_camera(int width, int height, RtbCamData *out) {
     out->delta_u.x = u.x; out->delta_u.y = u.y; out->delta_u.z = u.z;
     out->delta_v.x = v.x; out->delta_v.y = v.y; out->delta_v.z = v.z;
 }
+
+/* ---- display conversion, src/main.cu:343-371 -----------------------------------------------------
+ * `int colour = pixel * 255` is a float -> int conversion in host code: on x86-64 (cvttss2si) a NaN
+ * or an out-of-range product gives INT_MIN, which the clamp turns into 0.  Restated explicitly so
+ * that the result does not depend on the compiler's treatment of the undefined conversion. */
+void pto_display_rgba8(const float *rgb, int width, int height, unsigned char *rgba) {
+    for (size_t i = 0; i < (size_t)width * height; i++) {
+        for (int k = 0; k < 3; k++) {
+            float v = rgb[3 * i + k] * 255;
+            int colour = (v >= 2147483648.0f || v < -2147483648.0f || v != v) ? (-2147483647 - 1) : (int)v;
+            if (colour > 255) colour = 255;
+            else if (colour < 0) colour = 0;
+            rgba[4 * i + k] = (unsigned char)colour;
+        }
+        rgba[4 * i + 3] = 255;
+    }
+}

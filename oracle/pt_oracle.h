@@ -26,6 +26,9 @@ int pto_render(const PtoScene *s, const RtbCamData *cam, int width, int height, 
 int pto_primary_ids(const PtoScene *s, const RtbCamData *cam, int width, int height, int32_t *obj_id, int32_t *sub_id,
                     float *t, int nthreads);
 
+/* parse_pixel_colours, src/main.cu:343-371: float RGB -> RGBA8 (truncation, clamp to [0, 255], alpha 255) */
+void pto_display_rgba8(const float *rgb, int width, int height, unsigned char *rgba);
+
 /* known-answer hooks */
 unsigned int pto_seed(int array_index, int time_ms);
 float pto_rng(unsigned int *state);

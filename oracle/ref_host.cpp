@@ -30,6 +30,8 @@
 #include "gen/dispatch_part.inc"
 #include "gen/obj_read_part.inc"
 #include "gen/main_part.inc"
+namespace sf { typedef unsigned char Uint8; }  // the one SFML name parse_pixel_colours uses
+#include "gen/display_part.inc"
 #include "../ray-tracer_b200/host/scenes.hpp"
 #undef private
 #undef protected
@@ -340,6 +342,12 @@ void refh_primary_dir(int x, int y, float *dir3) {
     dir3[2] = r.direction.z;
 }
 int refh_inf() { return INF; }
+// parse_pixel_colours (src/main.cu:343-371) at the compiled resolution: in = W*H*3 floats, out = W*H*4 bytes
+void refh_display(const float *in, unsigned char *out) {
+    std::vector<float> v(in, in + (size_t)SCREEN_WIDTH * SCREEN_HEIGHT * 3);
+    std::vector<sf::Uint8> r = parse_pixel_colours(v);
+    std::memcpy(out, r.data(), r.size());
+}
 // struct sizes, for the record in DESIGN.md
 void refh_sizes(int *out, int n) {
     int v[] = {(int)sizeof(Vec3), (int)sizeof(Texture), (int)sizeof(Material), (int)sizeof(Sphere), (int)sizeof(Triangle),

@@ -118,6 +118,8 @@ lib.rtb_sync.argtypes = [_vp]
 lib.rtb_reset_accumulation.argtypes = [_vp]
 lib.rtb_set_accumulation.argtypes = [_vp, _vp, _i]
 lib.rtb_download.argtypes = [_vp, _vp, _ip]
+lib.rtb_display_rgba8.argtypes = [_vp, _vp]
+lib.rtb_write_ppm.argtypes = [_vp, ctypes.c_char_p]
 lib.rtb_device_image.argtypes = [_vp]
 lib.rtb_device_image.restype = _vp
 lib.rtb_stream.argtypes = [_vp]
@@ -268,6 +270,15 @@ class Tracer:
         f = ctypes.c_int()
         self._check(lib.rtb_download(self.ctx, _ptr(img), ctypes.byref(f)))
         return img, f.value
+
+    def display_rgba8(self):
+        """== parse_pixel_colours (src/main.cu:343-371) of the accumulation image, on the device."""
+        out = np.empty((self.height, self.width, 4), np.uint8)
+        self._check(lib.rtb_display_rgba8(self.ctx, _ptr(out)))
+        return out
+
+    def write_ppm(self, path):
+        self._check(lib.rtb_write_ppm(self.ctx, str(path).encode()))
 
     def device_ms(self):
         ms = ctypes.c_float()

@@ -51,6 +51,8 @@ struct rtb_ctx {
 
     // frame state
     float *d_image = nullptr;
+    unsigned char *d_rgba = nullptr;  // display conversion buffer (rtb_display_rgba8)
+    size_t rgba_pixels = 0;
     size_t image_floats = 0;
     int frame_num = 0;
     unsigned int *d_work = nullptr;
@@ -339,6 +341,21 @@ __global__ void shard_unpack_kernel(float *image, const float *gathered, int wid
     int band = lr / band_rows, within = lr - band * band_rows;
     int y = (band * world + rank) * band_rows + within;
     if (y < height) image[(size_t)y * row_floats + col] = gathered[i];
+}
+
+// parse_pixel_colours, src/main.cu:343-371.  The reference converts on the host with
+// `int colour = value * 255` (x86 cvttss2si: NaN / out of range -> INT_MIN -> clamped to 0).
+__global__ void display_rgba8_kernel(const float *image, uchar4 *rgba, size_t pixels) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    unsigned char out[3];
+    for (int k = 0; k < 3; k++) {
+        float v = image[3 * i + k] * 255;
+        int colour = (v >= 2147483648.0f || v < -2147483648.0f || v != v) ? (-2147483647 - 1) : (int)v;
+        colour = colour > 255 ? 255 : (colour < 0 ? 0 : colour);
+        out[k] = (unsigned char)colour;
+    }
+    rgba[i] = make_uchar4(out[0], out[1], out[2], 255);
 }
 
 int ensure_image(rtb_ctx *c) {
@@ -631,6 +648,7 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
     if (c->d_image) cudaFree(c->d_image);
+    if (c->d_rgba) cudaFree(c->d_rgba);
     if (c->d_work) cudaFree(c->d_work);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_wf_state) cudaFree(c->d_wf_state);
@@ -946,6 +964,40 @@ int rtb_download(rtb_ctx *c, float *rgb_host, int *frame_num_out) {
     RTB_CUDA(c, cudaMemcpyAsync(rgb_host, c->d_image, c->image_floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream), "copying image to host");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying image to host");
     if (frame_num_out) *frame_num_out = c->frame_num;
+    return 0;
+}
+
+int rtb_display_rgba8(rtb_ctx *c, uint8_t *rgba_host) {
+    if (!c || !rgba_host) return 1;
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    size_t pixels = c->image_floats / 3;
+    if (c->rgba_pixels != pixels) {
+        if (c->d_rgba) cudaFree(c->d_rgba);
+        c->d_rgba = nullptr; c->rgba_pixels = 0;
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_rgba, pixels * 4), "allocating display buffer");
+        c->rgba_pixels = pixels;
+    }
+    display_rgba8_kernel<<<(unsigned int)((pixels + 255) / 256), 256, 0, c->stream>>>(c->d_image, (uchar4 *)c->d_rgba, pixels);
+    RTB_CUDA(c, cudaGetLastError(), "launching display conversion");
+    RTB_CUDA(c, cudaMemcpyAsync(rgba_host, c->d_rgba, pixels * 4, cudaMemcpyDeviceToHost, c->stream), "copying display buffer to host");
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying display buffer to host");
+    return 0;
+}
+
+int rtb_write_ppm(rtb_ctx *c, const char *path) {
+    if (!c || !path) return 1;
+    std::vector<uint8_t> rgba((size_t)c->width * c->height * 4);
+    if (rgba.empty()) return fail(c, "rtb_write_ppm", "camera/resolution not set");
+    if (rtb_display_rgba8(c, rgba.data()) != 0) return 1;
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(c, "rtb_write_ppm", "cannot open the output file");
+    std::fprintf(f, "P6\n%d %d\n255\n", c->width, c->height);
+    std::vector<uint8_t> rgb((size_t)c->width * c->height * 3);
+    for (size_t i = 0; i < (size_t)c->width * c->height; i++) { rgb[3 * i] = rgba[4 * i]; rgb[3 * i + 1] = rgba[4 * i + 1]; rgb[3 * i + 2] = rgba[4 * i + 2]; }
+    size_t w = std::fwrite(rgb.data(), 1, rgb.size(), f);
+    std::fclose(f);
+    if (w != rgb.size()) return fail(c, "rtb_write_ppm", "short write");
     return 0;
 }
 

@@ -42,6 +42,7 @@ class Oracle:
             L.pto_normal.restype = ctypes.c_float
             L.pto_normal.argtypes = [ctypes.POINTER(ctypes.c_uint)]
             L.pto_default_camera.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(rtb.CamData)]
+            L.pto_display_rgba8.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
             L.pto_primary_dir.argtypes = [ctypes.POINTER(rtb.CamData), ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
             Oracle.lib = L
         desc = scene.desc if isinstance(scene, rtb.Scene) else scene
@@ -65,6 +66,17 @@ class Oracle:
         obj, sub, t = np.empty((h, w), np.int32), np.empty((h, w), np.int32), np.empty((h, w), np.float32)
         Oracle.lib.pto_primary_ids(self.scene, ctypes.byref(cam), w, h, _p(obj), _p(sub), _p(t), nthreads)
         return obj, sub, t
+
+
+def oracle_display_rgba8(image):
+    """parse_pixel_colours (src/main.cu:343-371) through the C oracle; image H x W x 3 float32"""
+    if Oracle.lib is None:
+        Oracle(rtb.SceneDesc())
+    image = np.ascontiguousarray(image, np.float32)
+    h, w = image.shape[:2]
+    out = np.empty((h, w, 4), np.uint8)
+    Oracle.lib.pto_display_rgba8(_p(image), w, h, _p(out))
+    return out
 
 
 def have_ref_host():

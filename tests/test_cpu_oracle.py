@@ -123,6 +123,38 @@ def test_reference_true_kernel_function_matches_row_loop():
     assert (a == b).all()
 
 
+def _display_probe(h, w):
+    """values that exercise every branch of the float -> byte conversion"""
+    rng = np.random.default_rng(7)
+    img = rng.uniform(-0.2, 1.3, size=(h, w, 3)).astype(np.float32)
+    special = np.array([0.0, -0.0, 1.0, 0.999999, 1.0 / 255, 254.999 / 255, 255.0 / 255, 256.0 / 255, 6.0, 1e9, 8.5e6, 3e38, -3e38,
+                        np.inf, -np.inf, np.nan, 1e-30, -1e-30, 0.5, 0.00392156], np.float32)
+    img.reshape(-1)[: special.size] = special
+    return img
+
+
+@needs_ref
+def test_display_conversion_equals_reference():
+    """pto_display_rgba8 against the reference's own parse_pixel_colours (src/main.cu:343-371),
+    compiled for the host at its built-in 1000x800."""
+    ref = ob.RefHost()
+    W, H = ref.L.refh_compiled_width(), ref.L.refh_compiled_height()
+    img = _display_probe(H, W)
+    want = np.empty((H, W, 4), np.uint8)
+    ref.L.refh_display(img.ctypes.data_as(ctypes.c_void_p), want.ctypes.data_as(ctypes.c_void_p))
+    got = ob.oracle_display_rgba8(img)
+    assert (got == want).all()
+    assert (got[..., 3] == 255).all()
+
+
+def test_display_conversion_known_answers():
+    img = np.zeros((1, 8, 3), np.float32)
+    img[0, :, 0] = [0.0, 1.0, 0.5, 2.0, -1.0, np.nan, np.inf, 254.999 / 255]
+    out = ob.oracle_display_rgba8(img)
+    # truncation (0.5 * 255 = 127.5 -> 127), clamp, and the x86 float->int result for NaN / inf (INT_MIN -> 0)
+    assert out[0, :, 0].tolist() == [0, 255, 127, 255, 0, 0, 0, 254]
+
+
 # ---------------------------------------------------------------- known answers (SURVEY.md App. A)
 def _oracle_lib():
     if ob.Oracle.lib is None:

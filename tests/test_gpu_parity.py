@@ -327,6 +327,30 @@ def test_sharded_rows_identical_to_full_frame(tracer, world, band):
     assert (combined == full).all()
 
 
+def test_display_conversion_and_ppm(tracer, tmp_path):
+    """rtb_display_rgba8 == parse_pixel_colours (src/main.cu:343-371): bit-exact bytes on a rendered
+    frame and on values that hit every branch (negative, > 1, NaN, inf, huge); PPM writer."""
+    scene = _scene(0, 0, 0)
+    Wd, Hd = 203, 151
+    tracer.setup(scene, Wd, Hd, 4, 5)
+    img = np.zeros((Hd, Wd, 3), np.float32)
+    tracer.render(img, 0, 7)
+    rgba = tracer.display_rgba8()
+    assert (rgba == ob.oracle_display_rgba8(img)).all()
+    assert rgba[..., :3].max() == 255 and rgba[..., :3].min() == 0  # the light saturates, the void is black
+    path = tmp_path / "frame.ppm"
+    tracer.write_ppm(path)
+    data = open(path, "rb").read()
+    header = f"P6\n{Wd} {Hd}\n255\n".encode()
+    assert data.startswith(header) and len(data) == len(header) + Wd * Hd * 3
+    assert (np.frombuffer(data[len(header):], np.uint8).reshape(Hd, Wd, 3) == rgba[..., :3]).all()
+    rng = np.random.default_rng(3)
+    probe = rng.uniform(-0.2, 1.3, size=(Hd, Wd, 3)).astype(np.float32)
+    probe.reshape(-1)[:12] = [0.0, -0.0, 1.0, 256.0 / 255, 6.0, 1e9, 3e38, -3e38, np.inf, -np.inf, np.nan, 254.999 / 255]
+    tracer.set_accumulation(probe, 1)
+    assert (tracer.display_rgba8() == ob.oracle_display_rgba8(probe)).all()
+
+
 def test_counters_match_oracle(tracer):
     scene = _scene(0, 0, 0)
     spp, bounces = 2, 5
