@@ -140,12 +140,27 @@ lib.rtb_measure_fp32_peak.argtypes = [_vp, ctypes.c_double, ctypes.POINTER(ctype
 scenes_lib.rtbs_build.restype = _vp
 scenes_lib.rtbs_build.argtypes = [_i, _i, _i, ctypes.c_char_p]
 scenes_lib.rtbs_desc.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+scenes_lib.rtbs_set_assets_dir.argtypes = [ctypes.c_char_p]
+scenes_lib.rtbs_set_assets_dir.restype = None
+scenes_lib.rtbs_load_obj_mtl.restype = _vp
+scenes_lib.rtbs_load_obj_mtl.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_float, ctypes.POINTER(ctypes.c_float * 3),
+                                         ctypes.POINTER(ctypes.c_float * 3)]
 scenes_lib.rtbs_use_sky.argtypes = [_vp]
 scenes_lib.rtbs_free.argtypes = [_vp]
 scenes_lib.rtbs_free.restype = None
 scenes_lib.rtbs_last_error.restype = ctypes.c_char_p
 scenes_lib.rtbs_default_camera.argtypes = [_i, _i, ctypes.POINTER(CamData)]
 scenes_lib.rtbs_render_settings.argtypes = [_i, _i, _i, _i, ctypes.POINTER(RenderData)]
+
+
+# enums of include/rtb.h
+TEX_COLOUR, TEX_GRADIENT, TEX_CHECKERBOARD, TEX_IMAGE = 0, 1, 2, 3
+MAT_STANDARD, MAT_EMISSIVE, MAT_REFRACTIVE = 0, 1, 2
+OBJ_SPHERE, OBJ_TRIANGLE, OBJ_QUAD, OBJ_ONE_WAY_QUAD, OBJ_CUBOID, OBJ_MESH = 0, 1, 2, 3, 4, 5
+
+# this repo's own fixtures (OBJ + MTL, images, parsed-texture files); host/obj_mtl.hpp reads the variable
+ASSETS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets")
+os.environ.setdefault("RTB_ASSETS_DIR", ASSETS_DIR)
 
 
 def models_dir():
@@ -162,10 +177,12 @@ class Scene:
     """One of the scene fixtures of host/scenes.hpp, built through the compat mirror of the reference API.
 
     ids: 0 Cornell+monkey+sphere (C1/C3/C5), 1 reflection, 2 textures, 3 glass, 4 seeded random spheres
-    (p0 = count, p1 = seed), 5 cube+spheres (C2), 6 monkey grid (C4; p0 x p1 instances).
+    (p0 = count, p1 = seed), 5 cube+spheres (C2), 6 monkey grid (C4; p0 x p1 instances), 7 studio.obj + studio.mtl
+    (per-face materials, vt, image texture from the parsed-texture file).
     """
 
-    def __init__(self, scene_id, p0=0, p1=0, models=None):
+    def __init__(self, scene_id, p0=0, p1=0, models=None, assets=None):
+        scenes_lib.rtbs_set_assets_dir((assets or os.environ.get("RTB_ASSETS_DIR") or ASSETS_DIR).encode())
         needs_models = scene_id in (0, 5, 6)
         mdir = (models or models_dir()) if needs_models else (models or "models")
         self.handle = scenes_lib.rtbs_build(scene_id, p0, p1, mdir.encode())
@@ -175,6 +192,22 @@ class Scene:
         scenes_lib.rtbs_desc(self.handle, ctypes.byref(self.desc))
         self.use_sky = bool(scenes_lib.rtbs_use_sky(self.handle))
         self.scene_id = scene_id
+
+    @classmethod
+    def from_obj(cls, obj_path, texture_dir=None, scale=1.0, rotate=(0.0, 0.0, 0.0), translate=(0.0, 0.0, 0.0)):
+        """An OBJ file with its MTL library (per-face materials, vt, map_Kd images from the parsed-texture
+        file in texture_dir) as a scene of MESH objects, one per material (host/obj_mtl.hpp)."""
+        self = cls.__new__(cls)
+        rot, tra = (ctypes.c_float * 3)(*rotate), (ctypes.c_float * 3)(*translate)
+        tdir = texture_dir or os.path.join(ASSETS_DIR, "textures")
+        self.handle = scenes_lib.rtbs_load_obj_mtl(str(obj_path).encode(), str(tdir).encode(), scale, ctypes.byref(rot), ctypes.byref(tra))
+        if not self.handle:
+            raise RtbError(scenes_lib.rtbs_last_error().decode())
+        self.desc = SceneDesc()
+        scenes_lib.rtbs_desc(self.handle, ctypes.byref(self.desc))
+        self.use_sky = True
+        self.scene_id = -1
+        return self
 
     def render_settings(self, spp, bounces, antialias=True):
         rd = RenderData()

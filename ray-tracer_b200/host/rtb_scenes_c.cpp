@@ -37,6 +37,36 @@ void *rtbs_build(int scene_id, int p0, int p1, const char *models_dir) {
     }
 }
 
+// directory of this repo's own fixtures (default: $RTB_ASSETS_DIR, else ray-tracer_b200/assets under cwd)
+void rtbs_set_assets_dir(const char *dir) { rtb_scenes::assets_dir() = dir; }
+
+// any OBJ (+ the MTL library it names, + map_Kd images from
+// <texture_dir>/parsed_textures.{bin,txt}) as a scene: the mesh is scaled / rotated / translated like
+// ObjFileMesh does (src/obj_read.cu:58-85) and split into one MESH object per material.
+void *rtbs_load_obj_mtl(const char *obj_path, const char *texture_dir, float scale, const float rotate_xyz[3], const float translate_xyz[3]) {
+    try {
+        rtb_compat::state().images.clear();
+        rtb_scenes::ObjMtlMesh m(obj_path);
+        m.enlarge(scale);
+        m.rotate(rotate_xyz[0], rotate_xyz[1], rotate_xyz[2]);
+        m.translate(translate_xyz[0], translate_xyz[1], translate_xyz[2]);
+        Material fallback = rtb_scenes::make_standard(Texture::create_const_colour(Vec3(1, 1, 1)), 0);
+        std::vector<Object> objects = m.create_objects(fallback, texture_dir);
+        Handle *h = new Handle();
+        rtb_compat::build_desc(objects.data(), (int)objects.size(), h->storage);
+        static std::vector<std::vector<float>> keep;
+        for (RtbImage &img : h->storage.images) {
+            keep.emplace_back(img.rgb, img.rgb + (size_t)img.width * img.height * 3);
+            img.rgb = keep.back().data();
+        }
+        h->use_sky = true;
+        return h;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+
 int rtbs_desc(void *handle, RtbSceneDesc *out) {
     if (!handle) return 1;
     *out = static_cast<Handle *>(handle)->storage.desc;

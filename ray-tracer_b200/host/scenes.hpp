@@ -54,6 +54,12 @@ inline Material make_refractive(Texture tex, float n) {
     return m;
 }
 
+}  // namespace rtb_scenes
+
+#include "obj_mtl.hpp"  // OBJ + MTL + vt loader, parsed-texture files (uses the helpers above)
+
+namespace rtb_scenes {
+
 // faces -> Triangle list, as SceneObjects::create_mesh does (src/main.cu:127-148):
 // 3-vertex faces become one Triangle, 4-vertex faces the two triangles of a Quad.
 inline void append_faces(std::vector<Triangle> &triangles, ObjFileMesh &obj, Material mat) {
@@ -247,6 +253,18 @@ inline void monkey_grid_scene(Scene &s, int nx, int ny) {
     s.objects.push_back(Object::create_quad(Vec3(-3, 2, 2.5), Vec3(3, 2, 2.5), Vec3(3, -2, 2.5), Vec3(-3, -2, 2.5), wall));
 }
 
+// id 7 -- SURVEY.md 8(f) row 1: an OBJ with an MTL library (four materials, two of them on quads with
+// `vt`, an image texture through the parsed-texture file) inside the Cornell box
+inline void studio_scene(Scene &s) {
+    create_cornell_box(s, Vec3(-0.5, 0.5, 1.2), 1, 1, 1, 0.5);
+    ObjMtlMesh m(assets_dir() + "/models/studio.obj");
+    m.enlarge(0.3);
+    m.rotate(0.05, 0.4, 0.03);
+    m.translate(0.0, -0.19, 1.7);
+    Material fallback = make_standard(Texture::create_const_colour(Vec3(1, 1, 1)), 0);
+    for (Object &o : m.create_objects(fallback, assets_dir() + "/textures")) s.objects.push_back(o);
+}
+
 // p0/p1: scene parameters (id 4: num_spheres, seed; id 6: nx, ny); 0 = default
 inline Scene build(int scene_id, int p0 = 0, int p1 = 0) {
     Scene s;
@@ -258,7 +276,8 @@ inline Scene build(int scene_id, int p0 = 0, int p1 = 0) {
         case 4: rand_sphere_scene(s, p0 > 0 ? p0 : 100, p1 > 0 ? (uint32_t)p1 : 2024u); break;
         case 5: cube_spheres_scene(s); break;
         case 6: monkey_grid_scene(s, p0 > 0 ? p0 : 40, p1 > 0 ? p1 : 35); break;
-        default: throw std::domain_error("Test scene must be a number between 0 and 6 (inclusive).\n");
+        case 7: studio_scene(s); break;
+        default: throw std::domain_error("Test scene must be a number between 0 and 7 (inclusive).\n");
     }
     return s;
 }

@@ -5,9 +5,10 @@ outputs of the reference's own source compiled for the host (oracle/_ref/libref_
 oracle/Makefile from /root/reference/src in place; nothing is copied).  Run in the build container
 (where /root/reference exists):
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py            # everything
+    python tests/golden/make_golden.py 7          # only the fixtures of the listed scene ids
 
-Per scene fixture (0..6): primary-hit ids / sub ids / distances with antialias off, and two
+Per scene fixture (0..7): primary-hit ids / sub ids / distances with antialias off, and two
 progressive frames of radiance at matched RNG streams.  kat.json holds the scalar known answers
 (seed, RNG stream, Box-Muller, camera, primary directions, struct sizes, INF).
 """
@@ -27,7 +28,7 @@ import oracle_binding as ob  # noqa: E402
 import raytracer_b200 as rtb  # noqa: E402
 
 # (scene id, p0, p1): the same list the GPU parity tests use
-SCENES = [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 0, 0), (4, 60, 7), (5, 0, 0), (6, 4, 3)]
+SCENES = [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 0, 0), (4, 60, 7), (5, 0, 0), (6, 4, 3), (7, 0, 0)]
 W, H, SPP, BOUNCES = 96, 80, 4, 5
 TIMES = (12345, 777)
 
@@ -35,7 +36,10 @@ TIMES = (12345, 777)
 def main():
     ref = ob.RefHost()
     L = ref.L
+    only = [int(a) for a in sys.argv[1:]]
     for sid, p0, p1 in SCENES:
+        if only and sid not in only:
+            continue
         ref.build_scene(sid, p0, p1)
         scene = rtb.Scene(sid, p0, p1)
         rd = scene.render_settings(SPP, BOUNCES)
@@ -49,6 +53,8 @@ def main():
                             obj=obj.astype(np.int16), sub=sub, t=t, frame0=f0, frame1=f1)
         print(f"scene {sid}: {int((obj >= 0).sum())} hit pixels, mean radiance {f1.mean():.6f}")
 
+    if only:
+        return
     kat = {}
     kat["inf"] = L.refh_inf()
     sizes = (ctypes.c_int * 32)()

@@ -21,7 +21,7 @@ import oracle_binding as ob
 import raytracer_b200 as rtb
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SCENES = [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 0, 0), (4, 60, 7), (5, 0, 0), (6, 4, 3)]
+SCENES = [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 0, 0), (4, 60, 7), (5, 0, 0), (6, 4, 3), (7, 0, 0)]
 KAT = json.load(open(os.path.join(GOLD, "kat.json")))
 
 
