@@ -154,6 +154,14 @@ int rtb_scene_add_mesh(rtb_ctx *ctx, const float *tri_points, const float *tri_u
  * (src/dispatch.cu:107), ReadOnlyDeviceArray<Object>/<Triangle> (src/main.cu:145,292) and the
  * host BVH constructor (src/objects.cu:452-464). */
 int rtb_scene_commit(rtb_ctx *ctx);
+/* Dynamic scenes (the reference builds its scene once, src/main.cu:290-295, and
+ * rebuilds every host BVH from scratch if it changes).  The context keeps the host description after a
+ * commit: replace the parameters of object `index` (non-mesh: any of the five simple types; mesh: only
+ * the material) or the triangles of a mesh (same count), then call rtb_scene_commit again: flatten +
+ * upload + GPU tree rebuild ("commit_ms" / "build_ms" of rtb_get_info report the cost).  Object order,
+ * hence the tie rule, is unchanged. */
+int rtb_scene_update_object(rtb_ctx *ctx, int index, const RtbObject *obj);
+int rtb_scene_update_mesh(rtb_ctx *ctx, int index, const float *tri_points, const float *tri_uv);
 /* rtb_scene_begin + one add per object of `desc` (same order) + rtb_scene_commit, in one call */
 int rtb_scene_set(rtb_ctx *ctx, const RtbSceneDesc *desc);
 /* view of the host-side description held by ctx (valid until the next rtb_scene_begin/destroy) */

@@ -101,6 +101,10 @@ lib.rtb_destroy.restype = None
 lib.rtb_set_camera.argtypes = [_vp, ctypes.POINTER(CamData), _i, _i]
 lib.rtb_set_render_data.argtypes = [_vp, ctypes.POINTER(RenderData)]
 lib.rtb_scene_set.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+lib.rtb_scene_desc.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
+lib.rtb_scene_commit.argtypes = [_vp]
+lib.rtb_scene_update_object.argtypes = [_vp, _i, ctypes.POINTER(Object)]
+lib.rtb_scene_update_mesh.argtypes = [_vp, _i, _vp, _vp]
 lib.rtb_scene_begin.argtypes = [_vp]
 lib.rtb_scene_commit.argtypes = [_vp]
 lib.rtb_scene_desc.argtypes = [_vp, ctypes.POINTER(SceneDesc)]
@@ -150,6 +154,9 @@ scenes_lib.rtbs_free.argtypes = [_vp]
 scenes_lib.rtbs_free.restype = None
 scenes_lib.rtbs_last_error.restype = ctypes.c_char_p
 scenes_lib.rtbs_default_camera.argtypes = [_i, _i, ctypes.POINTER(CamData)]
+scenes_lib.rtbs_camera.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_float * 3), ctypes.POINTER(ctypes.c_float * 3), ctypes.c_float,
+                                   ctypes.c_float, ctypes.POINTER(CamData)]
+scenes_lib.rtbs_camera.restype = None
 scenes_lib.rtbs_render_settings.argtypes = [_i, _i, _i, _i, ctypes.POINTER(RenderData)]
 
 
@@ -226,6 +233,15 @@ def default_camera(width, height):
     return cam
 
 
+def camera(width, height, pos=(0.0, 0.0, 0.0), rot=(0.0, 0.0, 0.0), fov=0.0, focal_len=0.0):
+    """Camera::assign_constant_mem's data (src/camera.cu:46-108) for any pose; rot in radians about x, y, z;
+    fov / focal_len 0 = the reference's defaults (60 degrees, 0.1)"""
+    cam = CamData()
+    p, r = (ctypes.c_float * 3)(*pos), (ctypes.c_float * 3)(*rot)
+    scenes_lib.rtbs_camera(width, height, ctypes.byref(p), ctypes.byref(r), fov, focal_len, ctypes.byref(cam))
+    return cam
+
+
 def _ptr(a):
     return a.ctypes.data_as(ctypes.c_void_p)
 
@@ -270,6 +286,25 @@ class Tracer:
         self.set_render_data(scene.render_settings(spp, bounces, antialias))
         self.set_scene(scene)
         return self
+
+    # dynamic scenes: edit the committed description in place, commit again
+    def scene_desc(self):
+        """view of the description the context holds (valid until the next scene begin / set)"""
+        d = SceneDesc()
+        self._check(lib.rtb_scene_desc(self.ctx, ctypes.byref(d)))
+        return d
+
+    def update_object(self, index, obj):
+        self._check(lib.rtb_scene_update_object(self.ctx, index, ctypes.byref(obj)))
+
+    def update_mesh(self, index, tri_points, tri_uv=None):
+        tri_points = np.ascontiguousarray(tri_points, np.float32)
+        if tri_uv is not None:
+            tri_uv = np.ascontiguousarray(tri_uv, np.float32)
+        self._check(lib.rtb_scene_update_mesh(self.ctx, index, _ptr(tri_points), _ptr(tri_uv) if tri_uv is not None else None))
+
+    def commit(self):
+        self._check(lib.rtb_scene_commit(self.ctx))
 
     def set_option(self, key, value):
         self._check(lib.rtb_set_option(self.ctx, key.encode(), int(value)))

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstring>
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <utility>
 #include <vector>
@@ -45,7 +46,7 @@ struct rtb_ctx {
     // device scene
     DScene d{};
     std::vector<void *> scene_allocs;
-    double build_ms = 0;
+    double build_ms = 0, commit_ms = 0;  // device time of the tree build / wall time of the whole commit
     size_t scene_bytes = 0;
     int culled_tris = 0;
 
@@ -763,8 +764,43 @@ int rtb_scene_add_mesh(rtb_ctx *c, const float *tri_points, const float *tri_uv,
     return idx;
 }
 
+// Dynamic scenes: the host description stays in the context after a commit,
+// so a frame loop edits objects in place and commits again (flatten + upload + GPU tree rebuild).
+int rtb_scene_update_object(rtb_ctx *c, int index, const RtbObject *o) {
+    if (!c || !o) return 1;
+    if (index < 0 || index >= (int)c->objects.size()) return fail(c, "rtb_scene_update_object", "object index out of range");
+    RtbObject &cur = c->objects[index];
+    if (o->material < 0 || o->material >= (int)c->materials.size()) return fail(c, "rtb_scene_update_object", "unknown material index");
+    if (cur.type == RTB_OBJ_MESH || o->type == RTB_OBJ_MESH) {
+        if (cur.type != o->type) return fail(c, "rtb_scene_update_object", "a mesh cannot change type (use rtb_scene_update_mesh for its triangles)");
+        cur.material = o->material;  // the triangle range of a mesh is owned by the context
+        return 0;
+    }
+    if (o->type < RTB_OBJ_SPHERE || o->type > RTB_OBJ_CUBOID) return fail(c, "rtb_scene_update_object", "unknown object type");
+    cur = *o;
+    return 0;
+}
+
+int rtb_scene_update_mesh(rtb_ctx *c, int index, const float *tri_points, const float *tri_uv) {
+    if (!c || !tri_points) return 1;
+    if (index < 0 || index >= (int)c->objects.size() || c->objects[index].type != RTB_OBJ_MESH) return fail(c, "rtb_scene_update_mesh", "not a mesh object");
+    const RtbObject &o = c->objects[index];
+    std::memcpy(&c->tri_points[(size_t)o.tri_first * 9], tri_points, (size_t)o.tri_count * 9 * sizeof(float));
+    if (tri_uv) std::memcpy(&c->tri_uv[(size_t)o.tri_first * 6], tri_uv, (size_t)o.tri_count * 6 * sizeof(float));
+    return 0;
+}
+
+static int scene_commit_timed(rtb_ctx *c);
+
 int rtb_scene_commit(rtb_ctx *c) {
     if (!c) return 1;
+    auto t0 = std::chrono::steady_clock::now();
+    int rc = scene_commit_timed(c);
+    c->commit_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return rc;
+}
+
+static int scene_commit_timed(rtb_ctx *c) {
     Bind b(c);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
@@ -1157,6 +1193,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "num_nodes") *value = c->d.num_bvh_prims > 1 ? c->d.num_bvh_prims - 1 : 0;
     else if (k == "num_large") *value = c->d.num_large;
     else if (k == "build_ms") *value = c->build_ms;
+    else if (k == "commit_ms") *value = c->commit_ms;
     else if (k == "kernel") *value = c->opt_kernel;
     else if (k == "wf_shade_ms") *value = c->wf_shade_ms;
     else if (k == "wf_traverse_ms") *value = c->wf_traverse_ms;

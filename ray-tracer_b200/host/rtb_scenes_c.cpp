@@ -85,6 +85,20 @@ void rtbs_default_camera(int width, int height, RtbCamData *out) {
                       rtb_compat::to_rtb(d.delta_v)};
 }
 
+// Camera at any pose: the members the reference marks "these values can be changed" (src/camera.cu:33-41)
+// -- position, rotations about x / y / z in radians, field of view in radians, focal length
+void rtbs_camera(int width, int height, const float pos[3], const float rot_xyz[3], float fov, float focal_len, RtbCamData *out) {
+    rtb_compat::set_resolution(width, height);
+    Camera cam;
+    cam.CAM_POS = Vec3(pos[0], pos[1], pos[2]);
+    cam.X_ROT = rot_xyz[0]; cam.Y_ROT = rot_xyz[1]; cam.Z_ROT = rot_xyz[2];
+    if (fov > 0) cam.FOV = fov;
+    if (focal_len > 0) cam.FOCAL_LEN = focal_len;
+    DeviceCamData d = cam.get_cam_data();
+    *out = RtbCamData{rtb_compat::to_rtb(d.cam_pos), rtb_compat::to_rtb(d.tl_pixel_pos), rtb_compat::to_rtb(d.delta_u),
+                      rtb_compat::to_rtb(d.delta_v)};
+}
+
 // src/main.cu:13,318-330
 void rtbs_render_settings(int use_sky, int spp, int bounces, int antialias, RtbRenderData *out) {
     RenderData r = rtb_scenes::render_settings(use_sky != 0, spp, bounces, antialias != 0);
