@@ -240,7 +240,7 @@ def main():
     ap.add_argument("--sharding", default="auto", choices=["auto", "tiles", "slices"])
     ap.add_argument("--ref-spp", type=int, default=8, help="spp per step of the reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront (library default)")
+    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront, 2 = timed choice between the two (library default)")
     ap.add_argument("--builder", type=int, default=None, help="0 = Karras LBVH, 1 = PLOC (library default)")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -279,8 +279,6 @@ def main():
     if args.builder is not None:
         tr.set_option("builder", args.builder)
     tr.setup(scene, W, H, spp, bounces)
-    kernel_kind = int(tr.info("kernel"))
-    per_frame = int(tr.info("launches_per_frame"))
     if tiles:
         tr.set_shard(rank, world, args.band_rows)
     ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
@@ -321,7 +319,7 @@ def main():
             """one step, everything resident: render my share, then the exchange"""
             tr.reset()
             tr.render_device(1, frame_time(k))
-            return per_frame + exchange()
+            exchange()
 
         # op mix / ray count of one step: counter build, same inputs, untimed
         tr.set_option("counters", 1)
@@ -340,6 +338,13 @@ def main():
         for k in range(args.warmup):
             device_step(k)
         barrier()
+        # with option "kernel" = 2 (the default) the first warm-up frame timed both variants on this rank's
+        # share of the workload and kept the faster; from here on the choice is fixed
+        kernel_kind = int(tr.info("kernel"))
+        per_frame = int(tr.info("launches_per_frame"))
+        tuned = (f"auto: {'wavefront' if kernel_kind == 1 else 'megakernel'} kept after timing both on a {min(spp, 8)}-spp frame "
+                 f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
+                 if int(tr.info("kernel_tuned")) else "fixed by --kernel")
         sampler = ClockSampler(local_rank)
         if rank == 0:
             sampler.start()
@@ -415,7 +420,7 @@ def main():
                        "sharding": "none" if world == 1 else (f"tiles: row-cyclic bands of {args.band_rows} rows of one frame, NCCL all-gather per frame" if tiles else
                                                                 f"sample slices: {world} frames of {spp} spp per step (one per rank, own time seed), NCCL all-reduce of the accumulation buffer per step"),
                        "kernel": ("wavefront: wf_shade + persistent wf_traverse per path segment" if kernel_kind == 1 else "persistent megakernel")
-                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
+                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "kernel_choice": tuned, "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
                        "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,

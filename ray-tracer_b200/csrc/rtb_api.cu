@@ -81,8 +81,16 @@ struct rtb_ctx {
     double wf_shade_ms = 0, wf_traverse_ms = 0, wf_total_ms = 0;
 
     // options
-    int opt_kernel = 1;  // 0 = persistent megakernel, 1 = wavefront (the measured winner)
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24, opt_walk_min = 16, opt_wf_refill = 8;
+    // 0 = persistent megakernel, 1 = wavefront, 2 = auto: both are timed on the first frame after the
+    // scene / resolution / settings / shard change and the faster is kept (they are bit-identical)
+    int opt_kernel = 2;
+    int auto_choice = -1;                  // -1 = not tuned yet
+    double tune_ms[2] = {0, 0};            // [0] megakernel, [1] wavefront: device ms of the tuning frame
+    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24;
+    // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (8, 12),
+    // whichever the tuning frame measures faster (closed rooms prefer the second, the 1 M-triangle grid the first)
+    int opt_walk_min = 0, opt_wf_refill = 0;
+    int tuned_wf_walk_min = 16, tuned_wf_refill = 8;
     int opt_builder = 1, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
@@ -375,8 +383,66 @@ int ensure_image(rtb_ctx *c) {
 
 int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num);
 
+int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num);
+
+// option "kernel" = 2: a short frame (RTB_TUNE_SPP samples per pixel of the real scene, camera, shard
+// and bounce limit) through each variant into a scratch image; the winner renders until something
+// that shapes the workload changes.  Which variant wins depends on the workload (long
+// paths in a closed room favour the wavefront kernels, short paths or few pixels per GPU the
+// megakernel); the images are bit-identical either way.
+#define RTB_TUNE_SPP 8
+int autotune_kernel(rtb_ctx *c) {
+    c->auto_choice = 1;
+    if (c->opt_counters || c->image_floats == 0) return 0;  // counted builds are not timed
+    float *scratch = nullptr;
+    if (cudaMalloc((void **)&scratch, c->image_floats * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;  // no room for a scratch image: keep the wavefront kernels
+    }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float *image = c->d_image;
+    const RtbRenderData rd = c->rd;
+    c->d_image = scratch;
+    int rc = 0;
+    // candidates: wavefront with two traversal policies, then the megakernel
+    struct Cand { int kern, walk_min, wf_refill; float ms; } cand[3] = {{1, 16, 8, 0.f}, {1, 8, 12, 0.f}, {0, 0, 0, 0.f}};
+    const int n_cand = 3;
+    for (int i = 0; i < n_cand && rc == 0; i++) {
+        if (cand[i].kern == 1) { c->tuned_wf_walk_min = cand[i].walk_min; c->tuned_wf_refill = cand[i].wf_refill; }
+        if (i == 1 && (c->opt_walk_min > 0 && c->opt_wf_refill > 0)) { cand[i].ms = 1e30f; continue; }  // both knobs pinned by the caller
+        for (int pass = (i == 1 ? 1 : 0); pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
+            c->rd.rays_per_pixel = pass == 0 ? 1 : std::min(rd.rays_per_pixel, RTB_TUNE_SPP);
+            cudaMemsetAsync(scratch, 0, c->image_floats * sizeof(float), c->stream);
+            cudaEventRecord(e0, c->stream);
+            rc = cand[i].kern == 1 ? launch_frame_wavefront(c, 12345, 0) : launch_frame_megakernel(c, 12345, 0);
+            cudaEventRecord(e1, c->stream);
+            if (rc == 0 && cudaStreamSynchronize(c->stream) != cudaSuccess) rc = fail(c, "tuning the kernel choice", cudaGetErrorString(cudaGetLastError()));
+            float ms = 0;
+            if (rc == 0) cudaEventElapsedTime(&ms, e0, e1);
+            cand[i].ms = ms;
+        }
+    }
+    int wf = cand[1].ms < cand[0].ms ? 1 : 0;
+    c->tuned_wf_walk_min = cand[wf].walk_min; c->tuned_wf_refill = cand[wf].wf_refill;
+    c->tune_ms[1] = cand[wf].ms; c->tune_ms[0] = cand[2].ms;
+    c->rd = rd;
+    c->d_image = image;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(scratch);
+    if (rc != 0) { c->auto_choice = -1; return rc; }
+    c->auto_choice = c->tune_ms[0] < 0.97 * c->tune_ms[1] ? 0 : 1;
+    return 0;
+}
+
+int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? 1 : c->auto_choice) : c->opt_kernel; }
+
 int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
-    if (c->opt_kernel == 1) return launch_frame_wavefront(c, time_ms, frame_num);
+    if (c->opt_kernel == 2 && c->auto_choice < 0 && autotune_kernel(c) != 0) return 1;
+    return effective_kernel(c) == 1 ? launch_frame_wavefront(c, time_ms, frame_num) : launch_frame_megakernel(c, time_ms, frame_num);
+}
+
+int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num) {
     RenderParams p;
     p.scene = c->d;
     std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
@@ -390,7 +456,7 @@ int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
     p.refill = c->opt_refill < 1 ? 1 : (c->opt_refill > 32 ? 32 : c->opt_refill);
-    p.walk_min = c->opt_walk_min < 1 ? 1 : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
+    p.walk_min = c->opt_walk_min < 1 ? 8 : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     p.work_counter = c->d_work;
     p.counters = c->opt_counters ? c->d_counters : nullptr;
     RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
@@ -449,8 +515,8 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     float4 *st = c->d_wf_state;
     base.st.A = st; base.st.B = st + slots; base.st.C = st + 2 * slots; base.st.O = st + 3 * slots; base.st.D = st + 4 * slots; base.st.H = st + 5 * slots;
     base.alive = c->d_wf_alive;
-    base.refill = c->opt_wf_refill < 1 ? 1 : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
-    base.walk_min = c->opt_walk_min < 1 ? 1 : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
+    base.refill = c->opt_wf_refill < 1 ? c->tuned_wf_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
+    base.walk_min = c->opt_walk_min < 1 ? c->tuned_wf_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     base.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
     int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
@@ -670,6 +736,7 @@ void rtb_destroy(rtb_ctx *c) {
 int rtb_set_camera(rtb_ctx *c, const RtbCamData *cam, int width, int height) {
     if (!c || !cam) return 1;
     if (width <= 0 || height <= 0 || (long long)width * height * 3 > 0x7fffffffLL) return fail(c, "rtb_set_camera", "bad resolution");
+    if (width != c->width || height != c->height) c->auto_choice = -1;  // a new pose keeps the tuned kernel choice, a new size does not
     c->cam = *cam;
     c->width = width; c->height = height;
     c->have_cam = true;
@@ -678,6 +745,7 @@ int rtb_set_camera(rtb_ctx *c, const RtbCamData *cam, int width, int height) {
 
 int rtb_set_render_data(rtb_ctx *c, const RtbRenderData *rd) {
     if (!c || !rd) return 1;
+    if (rd->rays_per_pixel != c->rd.rays_per_pixel || rd->reflection_limit != c->rd.reflection_limit) c->auto_choice = -1;
     c->rd = *rd;
     c->have_rd = true;
     return 0;
@@ -802,6 +870,7 @@ int rtb_scene_commit(rtb_ctx *c) {
 
 static int scene_commit_timed(rtb_ctx *c) {
     Bind b(c);
+    c->auto_choice = -1;
     cudaStreamSynchronize(c->stream);
     free_scene(c);
     Flat f;
@@ -1058,6 +1127,7 @@ int rtb_last_device_ms(rtb_ctx *c, float *ms_out) {
 int rtb_set_shard(rtb_ctx *c, int rank, int world, int band_rows) {
     if (!c) return 1;
     if (world < 1 || rank < 0 || rank >= world || band_rows < 1) return fail(c, "rtb_set_shard", "bad shard arguments");
+    if (world != c->shard_world || band_rows != c->band_rows) c->auto_choice = -1;
     c->shard_rank = rank; c->shard_world = world; c->band_rows = band_rows;
     return 0;
 }
@@ -1131,6 +1201,7 @@ int rtb_counters(rtb_ctx *c, RtbCounters *out) {
 int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     if (!c || !key) return 1;
     std::string k(key);
+    c->auto_choice = -1;  // every option shapes the kernels: tune again at the next frame
     if (k == "counters") c->opt_counters = value;
     else if (k == "traversal") c->opt_traversal = value;
     else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; }
@@ -1147,7 +1218,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "wf_streams") c->opt_wf_streams = value < 1 ? 1 : value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
     else if (k == "kernel") {
-        if (value != 0 && value != 1) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront");
+        if (value < 0 || value > 2) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice)");
         c->opt_kernel = value;
     }
     else if (k == "block_threads") {
@@ -1194,7 +1265,13 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "num_large") *value = c->d.num_large;
     else if (k == "build_ms") *value = c->build_ms;
     else if (k == "commit_ms") *value = c->commit_ms;
-    else if (k == "kernel") *value = c->opt_kernel;
+    else if (k == "kernel") *value = effective_kernel(c);      // the variant frames are rendered with
+    else if (k == "kernel_option") *value = c->opt_kernel;     // 0, 1 or 2 = auto
+    else if (k == "kernel_tuned") *value = c->opt_kernel == 2 && c->auto_choice >= 0 ? 1 : 0;
+    else if (k == "tune_megakernel_ms") *value = c->tune_ms[0];
+    else if (k == "tune_wavefront_ms") *value = c->tune_ms[1];
+    else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) == 1 ? c->tuned_wf_walk_min : 8);
+    else if (k == "wf_refill") *value = c->opt_wf_refill > 0 ? c->opt_wf_refill : c->tuned_wf_refill;
     else if (k == "wf_shade_ms") *value = c->wf_shade_ms;
     else if (k == "wf_traverse_ms") *value = c->wf_traverse_ms;
     else if (k == "wf_total_ms") *value = c->wf_total_ms;
@@ -1203,7 +1280,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
         double it = (double)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
         double rebuilds = c->opt_wf_rebuild > 0 && it > 0 ? std::floor((it - 1) / c->opt_wf_rebuild) : 0;
         int groups = std::max(1, std::min(c->opt_wf_groups, shard_local_rows(c, c->shard_rank)));
-        *value = c->opt_kernel == 1 ? groups * (1.0 + 2.0 * it + 3.0 * rebuilds) : 1.0;
+        *value = effective_kernel(c) == 1 ? groups * (1.0 + 2.0 * it + 3.0 * rebuilds) : 1.0;
     }
     else if (k.rfind("lane_stat", 0) == 0 && k.size() == 10 && k[9] >= '0' && k[9] <= '7') *value = (double)c->last_lane_stats[k[9] - '0'];
     else if (k == "scene_bytes") *value = (double)c->scene_bytes;

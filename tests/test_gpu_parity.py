@@ -123,7 +123,7 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
             f = tracer.render(img, f, 17)
             out.append((img, f, c))
     finally:
-        tracer.set_option("kernel", 1)  # library default
+        tracer.set_option("kernel", 2)  # library default
         tracer.set_option("counters", 0)
     assert out[0][1] == out[1][1] == 2
     assert (out[0][0] == out[1][0]).all()
@@ -187,7 +187,7 @@ def test_wavefront_sharded_and_odd_sizes(tracer):
         assert (a == b).all()
     finally:
         tracer.set_option("strict_fp", 0)
-        tracer.set_option("kernel", 1)  # library default
+        tracer.set_option("kernel", 2)  # library default
         tracer.set_shard(0, 1, 8)
 
 
@@ -326,6 +326,31 @@ def test_sharded_rows_identical_to_full_frame(tracer, world, band):
         combined[rows] = part[rows]
     tracer.set_shard(0, 1, 8)
     assert (combined == full).all()
+
+
+def test_auto_kernel_choice(tracer):
+    """option kernel = 2 (the default): the first frame times both variants on a short frame into a scratch
+    image and keeps the faster; the accumulation image is untouched by the tuning and the result is
+    bit-identical to either variant's."""
+    scene = _scene(0, 0, 0)
+    imgs = {}
+    try:
+        for kernel in (0, 2):
+            tracer.set_option("kernel", kernel)
+            tracer.setup(scene, W, H, 12, 5)
+            img = np.zeros((H, W, 3), np.float32)
+            assert tracer.render(img, 0, 99) == 1
+            tracer.render(img, 1, 100)
+            imgs[kernel] = img
+        assert int(tracer.info("kernel_option")) == 2 and int(tracer.info("kernel_tuned")) == 1
+        assert int(tracer.info("kernel")) in (0, 1)
+        assert tracer.info("tune_wavefront_ms") > 0 and tracer.info("tune_megakernel_ms") > 0
+        assert (imgs[0] == imgs[2]).all()
+        # a new resolution tunes again
+        tracer.setup(scene, 64, 48, 2, 3)
+        assert int(tracer.info("kernel_tuned")) == 0
+    finally:
+        tracer.set_option("kernel", 2)
 
 
 def test_display_conversion_and_ppm(tracer, tmp_path):
