@@ -355,6 +355,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
         unsigned tmask = __ballot_sync(FULL, mode == TRAVERSING);
         // leave the tree once `refill` lanes of the warp wait for the SHADE phase
         int quota = refill - __popc(__ballot_sync(FULL, mode == WAITING));
+#ifdef RTB_DYNAMIC_MASK
         if (mode == TRAVERSING) {
             if (!BRUTE) trav_run(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
             if (trav_done(T)) {
@@ -362,6 +363,15 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
                 pending = true;
             }
         }
+#else
+        // all 32 lanes enter together: WAITING and IDLE lanes hold a finished traversal state
+        // quota over the whole warp: the lanes that are not traversing now, plus max(1, refill - waiting) more
+        if (!BRUTE) trav_run(s, ray, T, FULL, (quota < 1 ? 1 : quota) + 32 - __popc(tmask), walk_min, cnt);
+        if (mode == TRAVERSING && trav_done(T)) {
+            mode = WAITING;
+            pending = true;
+        }
+#endif
     }
     if (COUNT && p.counters) {
         atomicAdd(p.counters + 0, n_seg);

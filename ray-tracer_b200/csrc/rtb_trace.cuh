@@ -264,8 +264,18 @@ __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &
 // The NODE phase goes on while at least `walk_min` lanes are walking; below that it ends as soon
 // as the other lanes have something better to do: a leaf to test, or -- when `quota` lanes have
 // finished their ray -- new rays to fetch (the call returns; quota <= 0 = run to completion).
+#ifdef RTB_DYNAMIC_MASK
+#define RTB_TRAV_MASK mask
+#else
+#define RTB_TRAV_MASK 0xffffffffu  // all 32 lanes call trav_run together: idle lanes hold a finished state (cur = RTB_DONE, leaf = 0)
+#endif
+// quota: leave once this many lanes of the WARP hold a finished (or no) ray; <= 0 = run to completion.
+// NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
+// traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
+template <int NODE_STEPS = 1>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
                                          Counters &cnt) {
+    (void)mask;
     int cur = T.cur, leaf = T.leaf, sp = T.sp;
     Best best = T.best;
     // every round retires at least one node step or one leaf of some lane; the cap only turns a
@@ -273,42 +283,45 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
     for (int round = 0; round < (1 << 22); round++) {
         unsigned finished;
         for (;;) {
-            bool walk = cur >= 0 && cur != RTB_DONE;
-            unsigned walking = __ballot_sync(mask, walk);
-            unsigned empty = __ballot_sync(mask, leaf == 0);
+            bool walk = (unsigned)cur < (unsigned)RTB_DONE;  // an internal node index
+            unsigned walking = __ballot_sync(RTB_TRAV_MASK, walk);
+            unsigned empty = __ballot_sync(RTB_TRAV_MASK, leaf == 0);
             // invariant: a leaf at the cursor implies a postponed leaf, so !walk && leaf == 0 means done
-            finished = mask & ~walking & empty;
+            finished = RTB_TRAV_MASK & ~walking & empty;
             if (!walking) break;
-            if (__popc(walking) < walk_min && ((mask & ~empty) || (quota > 0 && __popc(finished) >= quota))) break;
-            RTB_COUNT(cnt, node_iters); RTB_COUNT_N(cnt, node_lanes, __popc(walking)); RTB_COUNT_N(cnt, node_blocked, __popc(mask & ~walking & ~empty));
-            RTB_COUNT_N(cnt, node_done, __popc(finished)); RTB_COUNT_N(cnt, mask_lanes, __popc(mask));
-            if (walk) {
-                const float4 *N = s.nodes + 4 * cur;
-                float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
-                // relative slack on the distance cull: a primitive's own t carries more rounding
-                // than the box planes do (cancellation in Moller-Trumbore), so keep boxes that
-                // start a hair beyond the current best
-                float limit = best.t * 1.0001f;
-                float n0, n1;
-                RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
-                bool h0 = box_test(lo0, hi0, r, limit, n0);
-                bool h1 = box_test(lo1, hi1, r, limit, n1);
-                int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
-                // branch-free cursor update (selects, a predicated push, predicated pops): the
-                // four outcomes would otherwise run as four divergent paths
-                bool first0 = h0 && (!h1 || n0 <= n1);
-                int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
-                if (h0 && h1 && sp < RTB_STACK) T.stack[sp++] = far;
-                cur = near;
-                // stack[0] holds RTB_DONE as a sentinel (sp >= 1), so a pop is an unconditional load
-                if (!(h0 || h1)) { sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1); }
-                if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
-                    leaf = cur;
-                    sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
+            if (__popc(walking) < walk_min && ((RTB_TRAV_MASK & ~empty) || (quota > 0 && __popc(finished) >= quota))) break;
+            RTB_COUNT(cnt, node_iters); RTB_COUNT_N(cnt, node_lanes, __popc(walking)); RTB_COUNT_N(cnt, node_blocked, __popc(RTB_TRAV_MASK & ~walking & ~empty));
+            RTB_COUNT_N(cnt, node_done, __popc(finished)); RTB_COUNT_N(cnt, mask_lanes, __popc(RTB_TRAV_MASK));
+#pragma unroll
+            for (int step = 0; step < NODE_STEPS; step++) {
+                if ((unsigned)cur < (unsigned)RTB_DONE) {
+                    const float4 *N = s.nodes + 4 * cur;
+                    float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
+                    // relative slack on the distance cull: a primitive's own t carries more rounding
+                    // than the box planes do (cancellation in Moller-Trumbore), so keep boxes that
+                    // start a hair beyond the current best
+                    float limit = best.t * 1.0001f;
+                    float n0, n1;
+                    RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
+                    bool h0 = box_test(lo0, hi0, r, limit, n0);
+                    bool h1 = box_test(lo1, hi1, r, limit, n1);
+                    int r0 = __float_as_int(lo0.w), r1 = __float_as_int(lo1.w);
+                    // branch-free cursor update (selects, a predicated push, predicated pops): the
+                    // four outcomes would otherwise run as four divergent paths
+                    bool first0 = h0 && (!h1 || n0 <= n1);
+                    int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
+                    if (h0 && h1 && sp < RTB_STACK) T.stack[sp++] = far;
+                    cur = near;
+                    // stack[0] holds RTB_DONE as a sentinel (sp >= 1), so a pop is an unconditional load
+                    if (!(h0 || h1)) { sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1); }
+                    if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
+                        leaf = cur;
+                        sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
+                    }
                 }
             }
         }
-        RTB_COUNT(cnt, leaf_iters); RTB_COUNT_N(cnt, leaf_lanes, __popc(__ballot_sync(mask, leaf < 0)));
+        RTB_COUNT(cnt, leaf_iters); RTB_COUNT_N(cnt, leaf_lanes, __popc(__ballot_sync(RTB_TRAV_MASK, leaf < 0)));
         if (leaf < 0) {
             test_leaf(s, r, leaf, best, cnt);
             leaf = 0;
@@ -317,9 +330,9 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                 sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
             }
         }
-        unsigned alive = __ballot_sync(mask, cur != RTB_DONE || leaf < 0);
+        unsigned alive = __ballot_sync(RTB_TRAV_MASK, cur != RTB_DONE || leaf < 0);
         if (!alive) break;
-        if (quota > 0 && __popc(mask & ~alive) >= quota) break;
+        if (quota > 0 && __popc(RTB_TRAV_MASK & ~alive) >= quota) break;
     }
     T.cur = cur; T.leaf = leaf; T.sp = sp; T.best = best;
 }

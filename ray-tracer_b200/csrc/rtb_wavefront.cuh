@@ -209,11 +209,18 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
             if (exhausted) break;
             continue;
         }
+#ifdef RTB_DYNAMIC_MASK
         if (busy) {
             // while the queue has rays, leave the tree when `refill` lanes are free; afterwards run to the end
             int quota = exhausted ? 0 : p.refill - (32 - __popc(busy_mask));
             if (!BRUTE) trav_run(s, ray, T, busy_mask, exhausted ? 0 : (quota < 1 ? 1 : quota), p.walk_min, cnt);
         }
+#else
+        // all 32 lanes enter together (lanes without a ray hold a finished state): while the queue has
+        // rays, leave the tree when `refill` lanes are free; afterwards run to the end
+        // (the quota counts finished lanes of the whole warp: the lanes that are free now, plus at least one)
+        if (!BRUTE) trav_run<2>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
+#endif
     }
     if (COUNT && p.counters) {
         atomicAdd(p.counters + 2, cnt.box);

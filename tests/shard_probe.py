@@ -75,3 +75,10 @@ if __name__ == "__main__":
         kw = dict(sid=0, p0=0, p1=0, W=1920, H=1080, spp=256, bounces=8, reps=2)
         for o in ({"kernel": 1}, {"kernel": 1, "walk_min": 12}, {"kernel": 1, "walk_min": 8}, {"kernel": 1, "walk_min": 8, "wf_refill": 12}, {"kernel": 1, "walk_min": 12, "wf_refill": 12}):
             run(1, o, **kw)
+    if which == "ab":
+        kw = dict(sid=0, p0=0, p1=0, W=1920, H=1080, spp=64, bounces=8, reps=3)
+        run(1, {"kernel": 1}, **kw)
+        run(1, {"kernel": 1, "walk_min": 8, "wf_refill": 12}, **kw)
+        run(1, {"kernel": 0}, **kw)
+        run(1, {"kernel": 1})
+        run(8, {"kernel": 0})
