@@ -82,3 +82,8 @@ if __name__ == "__main__":
         run(1, {"kernel": 0}, **kw)
         run(1, {"kernel": 1})
         run(8, {"kernel": 0})
+    if which == "mega2":
+        run(8, {"kernel": 0})
+        run(1, {"kernel": 0})
+        run(8, {"kernel": 0}, sid=0, p0=0, p1=0, W=1920, H=1080, spp=64, bounces=8)
+        run(1, {"kernel": 0}, sid=5, p0=0, p1=0, W=1920, H=1080, spp=64, bounces=8)
