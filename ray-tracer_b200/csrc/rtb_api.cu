@@ -925,6 +925,7 @@ static int scene_commit_timed(rtb_ctx *c) {
         }
     }
     RTB_CUDA(c, upload(c, large_boxes, &d.large_boxes), "uploading large-primitive boxes");
+    for (size_t i = 0; i < 2 * RTB_MAX_LARGE; i++) d.large_box_c[i] = i < large_boxes.size() ? large_boxes[i] : make_float4(0, 0, 0, 0);
     RTB_CUDA(c, upload(c, large, &d.large_refs), "uploading large-primitive list");
     RTB_CUDA(c, upload(c, small, &d_small), "uploading tree primitive list");
     d.num_large = (int)large.size();

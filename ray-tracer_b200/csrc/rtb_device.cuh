@@ -36,6 +36,8 @@ struct DMaterial {
 };
 
 // ---- device scene (all pointers device memory, 16-byte aligned) --------------------------------
+#define RTB_MAX_LARGE 32  // the candidates of a ray are a 32-bit mask
+
 struct DScene {
     // LBVH: internal node i = 4 float4: {lo0.xyz, ref0} {hi0.xyz, -} {lo1.xyz, ref1} {hi1.xyz, -}
     // ref >= 0: internal node index; ref < 0: leaf, ~ref = (index << 3) | kind
@@ -48,6 +50,7 @@ struct DScene {
     // the tree and tested first, in a warp-uniform loop; their hits bound the tree traversal.
     const int *large_refs;
     const float4 *large_boxes;  // 2 float4 per large primitive: padded lo, hi
+    float4 large_box_c[2 * RTB_MAX_LARGE];  // the same boxes in the kernel parameters (constant bank: operands, not loads)
     int num_large;
     unsigned int large_sphere_mask;  // bit i: large primitive i is a sphere
     // triangles, 3 float4 each: {p0.xyz, s1.x} {s1.yz, s2.xy} {s2.z, n.xyz}.  KIND_TRI leaves

@@ -185,20 +185,49 @@ __device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, 
     for (int i = 0; i < s.num_large; i++) {
         float tn;
         RTB_COUNT(cnt, box);
-        if (box_test(__ldg(s.large_boxes + 2 * i), __ldg(s.large_boxes + 2 * i + 1), r, RTB_INF_F, tn)) cand |= 1u << i;
+        if (box_test(s.large_box_c[2 * i], s.large_box_c[2 * i + 1], r, RTB_INF_F, tn)) cand |= 1u << i;
     }
-    // triangles / quads first, then spheres: inside one loop every lane runs the same kind of test
+    // Triangles and quads: one Triangle::hit per lane and step, whatever the lane's candidate is (a
+    // single triangle, or triangle 1 / triangle 2 of a quad), so lanes with different candidate lists
+    // stay converged and the loop runs max-over-lanes(total triangle tests) steps.
     unsigned part = cand & ~s.large_sphere_mask;
-    cand &= s.large_sphere_mask;
-    for (int pass = 0; pass < 2; pass++) {
-        while (__any_sync(mask, part != 0)) {
-            if (part) {
-                int i = __ffs(part) - 1;
-                part &= part - 1;
-                test_leaf(s, r, __ldg(s.large_refs + i), best, cnt);
+    int tri = 0, left = 0;   // next triangle of the candidate in progress, triangles it still has
+    bool single = false;
+    while (__any_sync(mask, (part != 0) | (left > 0))) {
+        if (left == 0 && part) {
+            int i = __ffs(part) - 1;
+            part &= part - 1;
+            int enc = ~__ldg(s.large_refs + i), kind = enc & 7;
+            tri = enc >> RTB_KIND_BITS;
+            single = kind == KIND_TRI;
+            left = single ? 1 : 2;
+            if (kind >= KIND_QUAD_ONEWAY) {  // OneWayQuad::hit, objects.cu:273-280 (see test_leaf)
+                float4 c = __ldg(s.tris + 3 * tri + 2);
+                float m = (float)(1 - 2 * (kind == KIND_QUAD_ONEWAY_INV));
+                if (dot(r.d, v3(c.y * m, c.z * m, c.w * m)) < 0) left = 0;
             }
         }
-        part = cand;
+        if (left > 0) {
+            float t, u = 0, v = 0;
+            RTB_COUNT(cnt, tri);
+            bool hit = tri_test(s.tris + 3 * tri, r, t, u, v);
+            if (hit && single && (r.d.x == 0 || r.d.y == 0 || r.d.z == 0)) {
+                int leaf = __ldg(s.tri_refleaf + tri);
+                if (leaf >= 0 && !ref_path_hit(s, leaf, r)) hit = false;
+            }
+            if (hit) consider(s, best, t, u, v, tri << 1);
+            // Quad::hit, objects.cu:223-236: triangle 1 if it hits, else whatever triangle 2 says
+            left = hit ? 0 : left - 1;
+            tri++;
+        }
+    }
+    part = cand & s.large_sphere_mask;
+    while (__any_sync(mask, part != 0)) {
+        if (part) {
+            int i = __ffs(part) - 1;
+            part &= part - 1;
+            test_leaf(s, r, __ldg(s.large_refs + i), best, cnt);
+        }
     }
 }
 
