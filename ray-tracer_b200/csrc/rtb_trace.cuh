@@ -35,6 +35,9 @@ struct Counters {};
 // ---- Triangle::hit, objects.cu:135-163 ---------------------------------------------------------
 // T -> {p0.xyz, s1.x} {s1.yz, s2.xy} {s2.z, n.xyz}.  Early exits only skip work whose result the
 // reference discards (hit is a conjunction); t, u, v of an accepted hit are the reference's.
+// (Measured and rejected: fetching the 48-byte record with two requests -- a 256-bit + a 128-bit load
+// picked by the record's parity, or a 64-byte padded record with two 256-bit loads -- is 1-5 % slower
+// than three 128-bit loads: more registers in flight / more sectors, and the third word is needed last.)
 __device__ __forceinline__ bool tri_test(const float4 *__restrict__ T, const Ray &r, float &t, float &u, float &v) {
     float4 a = __ldg(T), b = __ldg(T + 1), c = __ldg(T + 2);
     V3 p0 = v3(a.x, a.y, a.z), side1 = v3(a.w, b.x, b.y), side2 = v3(b.z, b.w, c.x);
@@ -293,6 +296,20 @@ __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &
 // The NODE phase goes on while at least `walk_min` lanes are walking; below that it ends as soon
 // as the other lanes have something better to do: a leaf to test, or -- when `quota` lanes have
 // finished their ray -- new rays to fetch (the call returns; quota <= 0 = run to completion).
+// One 64-byte node.  sm_100a has 256-bit global loads (LDG.E.256): two requests per node visit instead
+// of four, which is what the L1 data pipe -- the limiter of the traversal kernel (ncu: 80 % busy,
+// 4.3 wavefronts per divergent request) -- is paid in.
+__device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &hi0, float4 &lo1, float4 &hi1) {
+#ifdef RTB_NODE_LDG128
+    lo0 = __ldg(N); hi0 = __ldg(N + 1); lo1 = __ldg(N + 2); hi1 = __ldg(N + 3);
+#else
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo0.x), "=f"(lo0.y), "=f"(lo0.z), "=f"(lo0.w), "=f"(hi0.x), "=f"(hi0.y), "=f"(hi0.z), "=f"(hi0.w) : "l"(N));
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo1.x), "=f"(lo1.y), "=f"(lo1.z), "=f"(lo1.w), "=f"(hi1.x), "=f"(hi1.y), "=f"(hi1.z), "=f"(hi1.w) : "l"(N + 2));
+#endif
+}
+
 #ifdef RTB_DYNAMIC_MASK
 #define RTB_TRAV_MASK mask
 #else
@@ -325,7 +342,8 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
             for (int step = 0; step < NODE_STEPS; step++) {
                 if ((unsigned)cur < (unsigned)RTB_DONE) {
                     const float4 *N = s.nodes + 4 * cur;
-                    float4 lo0 = __ldg(N), hi0 = __ldg(N + 1), lo1 = __ldg(N + 2), hi1 = __ldg(N + 3);
+                    float4 lo0, hi0, lo1, hi1;
+                    load_node(N, lo0, hi0, lo1, hi1);
                     // relative slack on the distance cull: a primitive's own t carries more rounding
                     // than the box planes do (cancellation in Moller-Trumbore), so keep boxes that
                     // start a hair beyond the current best

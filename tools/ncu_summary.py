@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Summarise an ncu report for profiles/: key raw metrics + per-function attribution.
-usage: ncu_summary.py <report.ncu-rep> <nvdisasm -gi sass> <mangled kernel substring> <title>"""
+usage: ncu_summary.py <report.ncu-rep> <nvdisasm -gi sass> <mangled kernel substring> <title> [kernel-name regex when the report holds several]"""
 import csv
 import io
 import os
@@ -8,7 +8,8 @@ import subprocess
 import sys
 
 rep, sass, kernel, title = sys.argv[1:5]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+ksel = ["-k", "regex:" + sys.argv[5]] if len(sys.argv) > 5 else []
+raw = subprocess.run(["ncu", "-i", rep] + ksel + ["--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[-1]
 want = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "sm__warps_active.avg.pct_of_peak_sustained_active",
@@ -26,7 +27,7 @@ for h, u, v in zip(hdr, units, vals):
 stalls = [(h, float(v)) for h, v in zip(hdr, vals) if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio") and v]
 stalls.sort(key=lambda kv: -kv[1])
 print("stall cycles per issued instruction: " + ", ".join(f"{h.split('stalled_')[1].split('_per_issue')[0]} {v:.2f}" for h, v in stalls[:8]))
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep] + ksel + ["--page", "source", "--csv"], capture_output=True, text=True).stdout
 tmp = "/tmp/_ncu_source.csv"
 open(tmp, "w").write(src)
 tool = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_by_line.py")
