@@ -87,7 +87,7 @@ struct rtb_ctx {
     int auto_choice = -1;                  // -1 = not tuned yet
     double tune_ms[2] = {0, 0};            // [0] megakernel, [1] wavefront: device ms of the tuning frame
     int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24;
-    // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (8, 12),
+    // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (12, 16),
     // whichever the tuning frame measures faster (closed rooms prefer the second, the 1 M-triangle grid the first)
     int opt_walk_min = 0, opt_wf_refill = 0;
     int tuned_wf_walk_min = 16, tuned_wf_refill = 8;
@@ -406,7 +406,7 @@ int autotune_kernel(rtb_ctx *c) {
     c->d_image = scratch;
     int rc = 0;
     // candidates: wavefront with two traversal policies, then the megakernel
-    struct Cand { int kern, walk_min, wf_refill; float ms; } cand[3] = {{1, 16, 8, 0.f}, {1, 8, 12, 0.f}, {0, 0, 0, 0.f}};
+    struct Cand { int kern, walk_min, wf_refill; float ms; } cand[3] = {{1, 16, 8, 0.f}, {1, 12, 16, 0.f}, {0, 0, 0, 0.f}};
     const int n_cand = 3;
     for (int i = 0; i < n_cand && rc == 0; i++) {
         if (cand[i].kern == 1) { c->tuned_wf_walk_min = cand[i].walk_min; c->tuned_wf_refill = cand[i].wf_refill; }

@@ -87,3 +87,11 @@ if __name__ == "__main__":
         run(1, {"kernel": 0})
         run(8, {"kernel": 0}, sid=0, p0=0, p1=0, W=1920, H=1080, spp=64, bounces=8)
         run(1, {"kernel": 0}, sid=5, p0=0, p1=0, W=1920, H=1080, spp=64, bounces=8)
+    if which == "grid":
+        kw = dict(sid=0, p0=0, p1=0, W=1920, H=1080, spp=128, bounces=8, reps=2)
+        for wm in (6, 8, 12, 16):
+            for rf in (8, 12, 16):
+                run(1, {"kernel": 1, "walk_min": wm, "wf_refill": rf}, **kw)
+        for rb in (8, 32):
+            run(1, {"kernel": 1, "walk_min": 8, "wf_refill": 12, "wf_rebuild": rb}, **kw)
+        run(1, {"kernel": 1, "walk_min": 8, "wf_refill": 12, "wf_groups": 3}, **kw)

@@ -65,7 +65,11 @@ rows = list(csv.reader(open(src_csv)))
 hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 hdr = rows[hdr_i]
 col = {n: i for i, n in enumerate(hdr)}
-body = rows[hdr_i + 1:]
+body = []
+for r in rows[hdr_i + 1:]:  # a filtered import prints the listing twice: stop at the second header
+    if not r or not r[0].startswith("0x"):
+        break
+    body.append(r)
 base = int(body[0][0], 16)
 by_line = defaultdict(lambda: [0, 0, 0])
 by_func = defaultdict(lambda: [0, 0, 0])
