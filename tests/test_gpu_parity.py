@@ -328,6 +328,47 @@ def test_sharded_rows_identical_to_full_frame(tracer, world, band):
     assert (combined == full).all()
 
 
+@pytest.mark.parametrize("scale,z", [(0.01, 60.0), (0.5, 900.0), (0.002, 3.0)])
+def test_far_and_tiny_trees(tracer, scale, z):
+    """A small mesh far from the camera and far from the world's origin (the box planes and the ray origin
+    then differ by many orders of magnitude: the regime where a conservative box test is easiest to get
+    wrong), and a tiny one close by: ids, distances and a frame must equal brute force over the primitives
+    bit for bit, strict and default builds, both kernel variants; strict ids equal the oracle's."""
+    import os
+    scene = rtb.Scene.from_obj(os.path.join(rtb.models_dir(), "low_poly_monkey.obj"), scale=scale, rotate=(0.1, 2.3, 0.05),
+                               translate=(0.3 * scale, -0.2 * scale, z))
+    fov = 2.2 * np.arctan(1.4 * scale / z)   # the mesh fills most of the frame
+    cam = rtb.camera(W, H, (0.0, 0.0, 0.0), (0.0, 0.0, 0.0), float(fov))
+    try:
+        for strict in (1, 0):
+            results = []
+            for traversal in (0, 1):
+                tracer.set_option("strict_fp", strict)
+                tracer.set_option("traversal", traversal)
+                tracer.set_camera(cam, W, H)
+                tracer.set_render_data(scene.render_settings(2, 3))
+                tracer.set_scene(scene)
+                obj, sub, t = tracer.primary_ids()
+                imgs = []
+                for kernel in (0, 1):
+                    tracer.set_option("kernel", kernel)
+                    img = np.zeros((H, W, 3), np.float32)
+                    tracer.render(img, 0, 31)
+                    imgs.append(img)
+                assert (imgs[0] == imgs[1]).all()
+                results.append((obj, sub, t, imgs[0]))
+            assert (results[0][0] >= 0).mean() > 0.2, "the mesh should cover a good part of the frame"
+            for a, b in zip(results[0], results[1]):
+                assert (a == b).all()
+            if strict:
+                o_obj, o_sub, o_t = ob.Oracle(scene).primary_ids(cam, W, H)
+                assert (results[0][0] == o_obj).all() and (results[0][1] == o_sub).all() and (results[0][2] == o_t).all()
+    finally:
+        tracer.set_option("strict_fp", 0)
+        tracer.set_option("traversal", 0)
+        tracer.set_option("kernel", 2)
+
+
 def test_auto_kernel_choice(tracer):
     """option kernel = 2 (the default): the first frame times both variants on a short frame into a scratch
     image and keeps the faster; the accumulation image is untouched by the tuning and the result is
