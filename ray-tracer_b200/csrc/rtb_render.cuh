@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
     Ray ray;
     ray.o = f.cam_o; ray.d = pdir; ray.inv = pdir;
     Trav T;
-    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0;
+    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0; T.top = RTB_DONE;
     T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
 
     for (;;) {

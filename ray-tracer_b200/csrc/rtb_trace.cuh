@@ -170,6 +170,8 @@ struct Trav {
     Best best;
     int cur;   // >= 0 internal node, < 0 leaf, RTB_DONE finished
     int leaf;  // postponed leaf (< 0) or 0
+    int top;   // the top of the stack, kept in a register: a pop then has no load on its critical path
+               // (the load that refills `top` is not needed before the NEXT pop); RTB_DONE = nothing left
     int sp;
     int stack[RTB_STACK];
 };
@@ -256,14 +258,13 @@ __device__ __forceinline__ void root_step(const DScene &s, const Ray &r, const B
 __device__ __forceinline__ void trav_start_below_root(Trav &T, int first, int second) {
     T.stack[0] = RTB_DONE;  // sentinel: popping an empty stack yields "finished"
     T.sp = 1;
-    if (second != 0) T.stack[T.sp++] = second;
+    T.top = second != 0 ? second : RTB_DONE;
     T.leaf = 0;
     T.cur = first;
     if (T.cur < 0) {  // a leaf: postpone it, go on with the other child
         T.leaf = T.cur;
-        T.sp--;
-        T.cur = T.stack[T.sp];
-        T.sp = max(T.sp, 1);
+        T.cur = T.top;
+        T.top = RTB_DONE;
     }
 }
 
@@ -271,6 +272,7 @@ __device__ __forceinline__ void trav_start_below_root(Trav &T, int first, int se
 __device__ __forceinline__ void trav_start(const DScene &s, Trav &T) {
     T.stack[0] = RTB_DONE;  // sentinel: popping an empty stack yields "finished"
     T.sp = 1;
+    T.top = RTB_DONE;
     T.leaf = 0;
     T.cur = s.num_bvh_prims > 0 ? s.root_ref : RTB_DONE;
     if (T.cur < 0) {  // a one-primitive tree: the root is a leaf
@@ -322,7 +324,7 @@ template <int NODE_STEPS = 1>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
                                          Counters &cnt) {
     (void)mask;
-    int cur = T.cur, leaf = T.leaf, sp = T.sp;
+    int cur = T.cur, leaf = T.leaf, sp = T.sp, top = T.top;
     Best best = T.best;
     // every round retires at least one node step or one leaf of some lane; the cap only turns a
     // logic error into a wrong pixel (caught by the parity tests) instead of a hung GPU
@@ -357,13 +359,14 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                     // four outcomes would otherwise run as four divergent paths
                     bool first0 = h0 && (!h1 || n0 <= n1);
                     int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
-                    if (h0 && h1 && sp < RTB_STACK) T.stack[sp++] = far;
+                    if (h0 && h1 && sp < RTB_STACK) { T.stack[sp++] = top; top = far; }
                     cur = near;
-                    // stack[0] holds RTB_DONE as a sentinel (sp >= 1), so a pop is an unconditional load
-                    if (!(h0 || h1)) { sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1); }
+                    // a pop takes the register-held top; stack[0] holds RTB_DONE as a sentinel (sp >= 1), so
+                    // the refill of `top` is an unconditional load
+                    if (!(h0 || h1)) { cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1); }
                     if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
                         leaf = cur;
-                        sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
+                        cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1);
                     }
                 }
             }
@@ -374,14 +377,14 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
             leaf = 0;
             if (cur < 0) {  // a second leaf was reached while the first was pending
                 leaf = cur;
-                sp = max(sp - 1, 0); cur = T.stack[sp]; sp = max(sp, 1);
+                cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1);
             }
         }
         unsigned alive = __ballot_sync(RTB_TRAV_MASK, cur != RTB_DONE || leaf < 0);
         if (!alive) break;
         if (quota > 0 && __popc(RTB_TRAV_MASK & ~alive) >= quota) break;
     }
-    T.cur = cur; T.leaf = leaf; T.sp = sp; T.best = best;
+    T.cur = cur; T.leaf = leaf; T.sp = sp; T.top = top; T.best = best;
 }
 
 // closest hit over the whole scene through the LBVH, in one go; `mask` = the calling lanes

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
     Ray ray;
     ray.o = v3(0, 0, 0); ray.d = v3(0, 0, 1); ray.inv = ray.d;
     Trav T;
-    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0;
+    T.cur = RTB_DONE; T.leaf = 0; T.sp = 0; T.top = RTB_DONE;
     T.best.t = RTB_INF_F; T.best.u = 0; T.best.v = 0; T.best.code = -1;
     int slot = -1;           // the ray this lane owns, -1 = none
     bool exhausted = false;  // the queue has nothing left (warp-uniform)
