@@ -343,7 +343,7 @@ def main():
         kernel_kind = int(tr.info("kernel"))
         per_frame = int(tr.info("launches_per_frame"))
         tuned = (f"auto: {'wavefront' if kernel_kind == 1 else 'megakernel'} kept after timing both on a {min(spp, 8)}-spp frame "
-                 f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms [2-wide {tr.info('tune_bvh2_ms'):.2f}, 4-wide {tr.info('tune_bvh4_ms'):.2f}], megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
+                 f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
                  if int(tr.info("kernel_tuned")) else "fixed by --kernel")
         sampler = ClockSampler(local_rank)
         if rank == 0:
@@ -420,8 +420,7 @@ def main():
                        "sharding": "none" if world == 1 else (f"tiles: row-cyclic bands of {args.band_rows} rows of one frame, NCCL all-gather per frame" if tiles else
                                                                 f"sample slices: {world} frames of {spp} spp per step (one per rank, own time seed), NCCL all-reduce of the accumulation buffer per step"),
                        "kernel": ("wavefront: wf_shade + persistent wf_traverse per path segment" if kernel_kind == 1 else "persistent megakernel")
-                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH")
-                                 + (", walked 4-wide" if int(tr.info("bvh_width")) == 4 else ", walked 2-wide"), "kernel_choice": tuned, "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
+                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "kernel_choice": tuned, "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
                        "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,

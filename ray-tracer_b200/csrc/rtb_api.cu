@@ -69,7 +69,7 @@ struct rtb_ctx {
     int *d_wf_block_count = nullptr;
     unsigned int *d_wf_counts = nullptr;
     size_t wf_slots = 0;
-    int wf_shade_per_sm = 0, wf_trav_per_sm = 0, wf_trav4_per_sm = 0;
+    int wf_shade_per_sm = 0, wf_trav_per_sm = 0;
     // option "wf_timing": CUDA events around every launch of the next frame (diagnostics only)
     int opt_wf_timing = 0;
     int opt_wf_rebuild = 16;  // iterations between queue rebuilds (0 = never)
@@ -86,14 +86,11 @@ struct rtb_ctx {
     int opt_kernel = 2;
     int auto_choice = -1;                  // -1 = not tuned yet
     double tune_ms[2] = {0, 0};            // [0] megakernel, [1] wavefront: device ms of the tuning frame
-    double tune_wide_ms[2] = {0, 0};       // wavefront over the binary / the 4-wide nodes (1e30 = not timed)
     int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24;
     // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (12, 16),
     // whichever the tuning frame measures faster (closed rooms prefer the second, the 1 M-triangle grid the first)
     int opt_walk_min = 0, opt_wf_refill = 0;
     int tuned_wf_walk_min = 16, tuned_wf_refill = 8;
-    // wf_traverse walks the binary nodes (2) or their 4-wide view (4); 0 = whichever the tuning frame measures faster
-    int opt_bvh_width = 0, tuned_wide = 0;
     int opt_builder = 1, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
@@ -408,19 +405,13 @@ int autotune_kernel(rtb_ctx *c) {
     const RtbRenderData rd = c->rd;
     c->d_image = scratch;
     int rc = 0;
-    // candidates: wavefront with two traversal policies over the binary and the 4-wide nodes, then the megakernel
-    struct Cand { int kern, walk_min, wf_refill, wide; float ms; bool warm; } cand[5] = {
-        {1, 16, 8, 0, 0.f, true}, {1, 12, 16, 0, 0.f, false}, {1, 16, 8, 1, 0.f, true}, {1, 12, 16, 1, 0.f, false}, {0, 0, 0, 0, 0.f, true}};
-    const int n_cand = 5;
-    const bool policy_pinned = c->opt_walk_min > 0 && c->opt_wf_refill > 0;
+    // candidates: wavefront with two traversal policies, then the megakernel
+    struct Cand { int kern, walk_min, wf_refill; float ms; } cand[3] = {{1, 16, 8, 0.f}, {1, 12, 16, 0.f}, {0, 0, 0, 0.f}};
+    const int n_cand = 3;
     for (int i = 0; i < n_cand && rc == 0; i++) {
-        cand[i].ms = 1e30f;
-        if (cand[i].kern == 1) {
-            if (policy_pinned && !cand[i].warm) continue;  // both knobs pinned by the caller: one policy to time
-            if (cand[i].wide ? (c->opt_bvh_width == 2 || !c->d.nodes4) : (c->opt_bvh_width == 4 && c->d.nodes4)) continue;
-            c->tuned_wf_walk_min = cand[i].walk_min; c->tuned_wf_refill = cand[i].wf_refill; c->tuned_wide = cand[i].wide;
-        }
-        for (int pass = (cand[i].warm ? 0 : 1); pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
+        if (cand[i].kern == 1) { c->tuned_wf_walk_min = cand[i].walk_min; c->tuned_wf_refill = cand[i].wf_refill; }
+        if (i == 1 && (c->opt_walk_min > 0 && c->opt_wf_refill > 0)) { cand[i].ms = 1e30f; continue; }  // both knobs pinned by the caller
+        for (int pass = (i == 1 ? 1 : 0); pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
             c->rd.rays_per_pixel = pass == 0 ? 1 : std::min(rd.rays_per_pixel, RTB_TUNE_SPP);
             cudaMemsetAsync(scratch, 0, c->image_floats * sizeof(float), c->stream);
             cudaEventRecord(e0, c->stream);
@@ -432,12 +423,9 @@ int autotune_kernel(rtb_ctx *c) {
             cand[i].ms = ms;
         }
     }
-    int wf = 0;
-    for (int i = 1; i < 4; i++)
-        if (cand[i].ms < cand[wf].ms) wf = i;
-    c->tuned_wf_walk_min = cand[wf].walk_min; c->tuned_wf_refill = cand[wf].wf_refill; c->tuned_wide = cand[wf].wide;
-    c->tune_ms[1] = cand[wf].ms; c->tune_ms[0] = cand[4].ms;
-    c->tune_wide_ms[0] = std::min(cand[0].ms, cand[1].ms); c->tune_wide_ms[1] = std::min(cand[2].ms, cand[3].ms);
+    int wf = cand[1].ms < cand[0].ms ? 1 : 0;
+    c->tuned_wf_walk_min = cand[wf].walk_min; c->tuned_wf_refill = cand[wf].wf_refill;
+    c->tune_ms[1] = cand[wf].ms; c->tune_ms[0] = cand[2].ms;
     c->rd = rd;
     c->d_image = image;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
@@ -509,9 +497,8 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     }
     if (!c->d_wf_counts) RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_counts, 16 * sizeof(unsigned int)), "allocating wavefront counters");
     if (c->wf_shade_per_sm == 0) {
-        cudaError_t e = c->opt_strict ? strict::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm, &c->wf_trav4_per_sm)
-                                       : fast::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm, &c->wf_trav4_per_sm);
-        if (e != cudaSuccess || c->wf_shade_per_sm <= 0 || c->wf_trav_per_sm <= 0 || c->wf_trav4_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
+        cudaError_t e = c->opt_strict ? strict::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm) : fast::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm);
+        if (e != cudaSuccess || c->wf_shade_per_sm <= 0 || c->wf_trav_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
     }
     WfParams base;
     base.scene = c->d;
@@ -532,9 +519,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     base.walk_min = c->opt_walk_min < 1 ? c->tuned_wf_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     base.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
-    base.wide = (c->opt_bvh_width == 4 || (c->opt_bvh_width == 0 && c->tuned_wide)) && c->d.nodes4 && !brute ? 1 : 0;
-    const int trav_limit = base.wide ? c->wf_trav4_per_sm : c->wf_trav_per_sm;
-    int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, trav_limit) : trav_limit;
+    int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
     const int trav_blocks = c->num_sms * trav_per_sm;
     const long long iterations = (long long)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
     const long long rebuild_every = c->opt_wf_rebuild;
@@ -961,8 +946,6 @@ static int scene_commit_timed(rtb_ctx *c) {
     int root = 0;
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "timing LBVH build");
     RTB_CUDA(c, lbvh_build(in, &nodes, &root, c->stream, c->opt_builder, c->opt_ploc_radius), "building LBVH");
-    float4 *nodes4 = nullptr;
-    RTB_CUDA(c, lbvh_collapse4(nodes, d.num_bvh_prims - 1, &nodes4, c->stream), "building the 4-wide nodes");
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "timing LBVH build");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "building LBVH");
     float ms = 0;
@@ -972,12 +955,7 @@ static int scene_commit_timed(rtb_ctx *c) {
         c->scene_allocs.push_back(nodes);
         c->scene_bytes += sizeof(float4) * 4 * (size_t)(d.num_bvh_prims - 1);
     }
-    if (nodes4) {
-        c->scene_allocs.push_back(nodes4);
-        c->scene_bytes += sizeof(float4) * 8 * (size_t)(d.num_bvh_prims - 1);
-    }
     d.nodes = nodes;
-    d.nodes4 = nodes4;
     d.root_ref = root;
     for (int k = 0; k < 4; k++) d.root_node[k] = make_float4(0, 0, 0, 0);
     if (nodes && root >= 0)
@@ -1240,10 +1218,6 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "wf_groups") c->opt_wf_groups = value < 1 ? 1 : value;
     else if (k == "wf_streams") c->opt_wf_streams = value < 1 ? 1 : value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
-    else if (k == "bvh_width") {
-        if (value != 0 && value != 2 && value != 4) return fail(c, "rtb_set_option", "bvh_width: 2 = binary nodes, 4 = 4-wide nodes, 0 = auto (timed choice); wavefront traversal only");
-        c->opt_bvh_width = value;
-    }
     else if (k == "kernel") {
         if (value < 0 || value > 2) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice)");
         c->opt_kernel = value;
@@ -1295,9 +1269,6 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "kernel") *value = effective_kernel(c);      // the variant frames are rendered with
     else if (k == "kernel_option") *value = c->opt_kernel;     // 0, 1 or 2 = auto
     else if (k == "kernel_tuned") *value = c->opt_kernel == 2 && c->auto_choice >= 0 ? 1 : 0;
-    else if (k == "bvh_width") *value = effective_kernel(c) == 1 && c->d.nodes4 && (c->opt_bvh_width == 4 || (c->opt_bvh_width == 0 && c->tuned_wide)) ? 4 : 2;
-    else if (k == "tune_bvh2_ms") *value = c->tune_wide_ms[0];
-    else if (k == "tune_bvh4_ms") *value = c->tune_wide_ms[1];
     else if (k == "tune_megakernel_ms") *value = c->tune_ms[0];
     else if (k == "tune_wavefront_ms") *value = c->tune_ms[1];
     else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) == 1 ? c->tuned_wf_walk_min : 8);

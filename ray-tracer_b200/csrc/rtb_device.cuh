@@ -42,9 +42,6 @@ struct DScene {
     // LBVH: internal node i = 4 float4: {lo0.xyz, ref0} {hi0.xyz, -} {lo1.xyz, ref1} {hi1.xyz, -}
     // ref >= 0: internal node index; ref < 0: leaf, ~ref = (index << 3) | kind
     const float4 *nodes;
-    // the same tree seen 4-wide (rtb_lbvh.cu, collapse4_kernel): node i = 8 float4, child k =
-    // {lo.xyz, ref} {hi.xyz, -}, indexed by the binary node index; nullptr = not built
-    const float4 *nodes4;
     int num_prims;       // all primitives (leaves of the LBVH + large primitives)
     int num_bvh_prims;   // leaves of the LBVH
     int root_ref;        // encoded like a child ref (a 1-primitive tree has a leaf root)

@@ -56,7 +56,6 @@ struct WfParams {
     unsigned int *tn, *tn_next; // its length (wf_shade appends, wf_traverse reads) / the counter wf_traverse zeroes for the next wf_shade
     int first;                  // wf_shade: 1 = no hit to consume yet (start of the frame)
     int refill, walk_min;
-    int wide;                   // wf_traverse: 1 = walk the 4-wide view of the tree (scene.nodes4)
     unsigned long long *counters;
 };
 
@@ -71,7 +70,7 @@ struct LaunchConfig {
     cudaError_t render_occupancy(int threads, int *blocks_per_sm);                                                  \
     cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);                     \
     cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
-    cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm, int *traverse4_blocks_per_sm);                              \
+    cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \
     cudaError_t launch_wf_rebuild(int slot_base, int n_slots, const unsigned char *alive, int *block_count, int *queue, unsigned int *total, cudaStream_t st); \
     }
 RTB_DECLARE_VARIANT(fast)

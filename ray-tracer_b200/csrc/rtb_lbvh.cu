@@ -488,59 +488,4 @@ done:
     return err;
 }
 
-// ---- 4-wide nodes --------------------------------------------------------------------------------
-// One 128-byte node per BINARY node i, at the same index: the children of i with up to two of them
-// opened (replaced by their own two children), the larger box first -- the greedy surface-area
-// collapse of a binary tree into a 4-wide one (Wald et al. 2008), done for every binary node
-// independently so that no renumbering is needed: any binary node index (the root step's children,
-// a 4-wide node's children) is also a valid entry into the 4-wide array.  Nodes that were opened
-// into their parent are simply never visited.
-// Layout, 8 float4: child k = {lo.xyz, ref} {hi.xyz, 0}; an empty slot is a box at a far-away point
-// (no ray reaches it inside any distance limit, whatever its direction) with ref = 0x7fffffff.
-__global__ void collapse4_kernel(int num_internal, const float4 *__restrict__ nodes, float4 *__restrict__ nodes4) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= num_internal) return;
-    float4 lo[4], hi[4];
-    int count = 2;
-    lo[0] = nodes[4 * (size_t)i]; hi[0] = nodes[4 * (size_t)i + 1];
-    lo[1] = nodes[4 * (size_t)i + 2]; hi[1] = nodes[4 * (size_t)i + 3];
-    for (int round = 0; round < 2; round++) {
-        int pick = -1;
-        float pick_area = -1.f;
-        for (int k = 0; k < count; k++) {
-            if (__float_as_int(lo[k].w) < 0) continue;  // a leaf stays
-            float ex = hi[k].x - lo[k].x, ey = hi[k].y - lo[k].y, ez = hi[k].z - lo[k].z;
-            float area = ex * ey + ey * ez + ez * ex;
-            if (!(area <= pick_area)) { pick = k; pick_area = area; }  // NaN areas are picked too
-        }
-        if (pick < 0) break;
-        size_t c = (size_t)__float_as_int(lo[pick].w);
-        lo[pick] = nodes[4 * c]; hi[pick] = nodes[4 * c + 1];
-        lo[count] = nodes[4 * c + 2]; hi[count] = nodes[4 * c + 3];
-        count++;
-    }
-    for (int k = count; k < 4; k++) {
-        lo[k] = make_float4(3e38f, 3e38f, 3e38f, __int_as_float(0x7fffffff));
-        hi[k] = make_float4(3e38f, 3e38f, 3e38f, 0.f);
-    }
-    for (int k = 0; k < 4; k++) {
-        hi[k].w = 0.f;
-        nodes4[8 * (size_t)i + 2 * k] = lo[k];
-        nodes4[8 * (size_t)i + 2 * k + 1] = hi[k];
-    }
-}
-
-cudaError_t lbvh_collapse4(const float4 *nodes, int num_internal, float4 **nodes4_out, cudaStream_t st) {
-    *nodes4_out = nullptr;
-    if (!nodes || num_internal <= 0) return cudaSuccess;
-    float4 *out = nullptr;
-    cudaError_t e = cudaMalloc(&out, sizeof(float4) * 8 * (size_t)num_internal);
-    if (e != cudaSuccess) return e;
-    collapse4_kernel<<<(num_internal + 255) / 256, 256, 0, st>>>(num_internal, nodes, out);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) { cudaFree(out); return e; }
-    *nodes4_out = out;
-    return cudaSuccess;
-}
-
 }  // namespace rtb

@@ -17,8 +17,4 @@ struct LbvhInput {
 // quality) with search radius `ploc_radius` over the same Morton order.
 cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st, int builder, int ploc_radius);
 
-// The 4-wide view of the same tree (see collapse4_kernel): *nodes4_out = cudaMalloc'd num_internal * 8
-// float4 (caller frees), nullptr when there are no internal nodes.  Runs on `st`, does not synchronise.
-cudaError_t lbvh_collapse4(const float4 *nodes, int num_internal, float4 **nodes4_out, cudaStream_t st);
-
 }  // namespace rtb

@@ -162,7 +162,6 @@ __device__ __forceinline__ bool box_test(float4 lo, float4 hi, const Ray &r, flo
 #endif
 
 #define RTB_DONE 0x7fffffff
-#define RTB_MISS_KEY 3e38f  // sort key of a child box the ray misses (4-wide node step)
 
 // Resumable traversal state of one ray: lives in the lane across iterations of the megakernel's
 // scheduling loop, so that lanes whose rays end early can go and shade / fetch new rays while the
@@ -321,11 +320,7 @@ __device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &
 // quota: leave once this many lanes of the WARP hold a finished (or no) ray; <= 0 = run to completion.
 // NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
 // traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
-// WIDE: the node step reads the 4-wide view of the tree (DScene::nodes4): four slab tests, the hits
-// sorted by entry distance (a 5-exchange network over (distance, ref) pairs, misses last), the nearest
-// becomes the cursor and the others are pushed far to near.  Half as many dependent node fetches per
-// ray; everything else (postponed leaves, quota, walk_min, the resumable state) is shared.
-template <int NODE_STEPS = 1, bool WIDE = false>
+template <int NODE_STEPS = 1>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
                                          Counters &cnt) {
     (void)mask;
@@ -347,34 +342,7 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
             RTB_COUNT_N(cnt, node_done, __popc(finished)); RTB_COUNT_N(cnt, mask_lanes, __popc(RTB_TRAV_MASK));
 #pragma unroll
             for (int step = 0; step < NODE_STEPS; step++) {
-                if (WIDE) {
-                    if ((unsigned)cur < (unsigned)RTB_DONE) {
-                        float4 c0l, c0h, c1l, c1h, c2l, c2h, c3l, c3h;
-                        load_node(s.nodes4 + 8 * (size_t)cur, c0l, c0h, c1l, c1h);
-                        load_node(s.nodes4 + 8 * (size_t)cur + 4, c2l, c2h, c3l, c3h);
-                        float limit = best.t * 1.0001f;
-                        float k0, k1, k2, k3;
-                        RTB_COUNT(cnt, box); RTB_COUNT(cnt, box); RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
-                        // a miss sorts behind every hit (entry distances are <= limit <= 2^30 * 1.0001)
-                        if (!box_test(c0l, c0h, r, limit, k0)) k0 = RTB_MISS_KEY;
-                        if (!box_test(c1l, c1h, r, limit, k1)) k1 = RTB_MISS_KEY;
-                        if (!box_test(c2l, c2h, r, limit, k2)) k2 = RTB_MISS_KEY;
-                        if (!box_test(c3l, c3h, r, limit, k3)) k3 = RTB_MISS_KEY;
-                        int r0 = __float_as_int(c0l.w), r1 = __float_as_int(c1l.w), r2 = __float_as_int(c2l.w), r3 = __float_as_int(c3l.w);
-#define RTB_CE(ka, ra, kb, rb) { bool sw_ = kb < ka; float kt_ = sw_ ? ka : kb; ka = sw_ ? kb : ka; kb = kt_; int rt_ = sw_ ? ra : rb; ra = sw_ ? rb : ra; rb = rt_; }
-                        RTB_CE(k0, r0, k1, r1) RTB_CE(k2, r2, k3, r3) RTB_CE(k0, r0, k2, r2) RTB_CE(k1, r1, k3, r3) RTB_CE(k1, r1, k2, r2)
-#undef RTB_CE
-                        if (k3 < RTB_MISS_KEY && sp < RTB_STACK) { T.stack[sp++] = top; top = r3; }
-                        if (k2 < RTB_MISS_KEY && sp < RTB_STACK) { T.stack[sp++] = top; top = r2; }
-                        if (k1 < RTB_MISS_KEY && sp < RTB_STACK) { T.stack[sp++] = top; top = r1; }
-                        cur = r0;
-                        if (!(k0 < RTB_MISS_KEY)) { cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1); }
-                        if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
-                            leaf = cur;
-                            cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1);
-                        }
-                    }
-                } else if ((unsigned)cur < (unsigned)RTB_DONE) {
+                if ((unsigned)cur < (unsigned)RTB_DONE) {
                     const float4 *N = s.nodes + 4 * cur;
                     float4 lo0, hi0, lo1, hi1;
                     load_node(N, lo0, hi0, lo1, hi1);

@@ -29,12 +29,6 @@
 #ifndef RTB_TRAV_MIN_BLOCKS
 #define RTB_TRAV_MIN_BLOCKS 8
 #endif
-#ifndef RTB_TRAV4_MIN_BLOCKS
-#define RTB_TRAV4_MIN_BLOCKS 6  // the 4-wide node step holds four boxes in flight: 80 registers
-#endif
-#ifndef RTB_TRAV4_NODE_STEPS
-#define RTB_TRAV4_NODE_STEPS 1
-#endif
 
 __device__ __forceinline__ void wf_slot_to_pixel(const WfParams &p, int slot, int &x, int &y) {
     int ly = slot / p.width;
@@ -152,8 +146,8 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
 
 // Persistent traversal: every lane owns one ray at a time; finished lanes store their hit and
 // fetch the next ray as soon as `refill` of them are waiting (or nobody traverses any more).
-template <bool BRUTE, bool COUNT, bool WIDE>
-__global__ void __launch_bounds__(RTB_BLOCK_THREADS, WIDE ? RTB_TRAV4_MIN_BLOCKS : RTB_TRAV_MIN_BLOCKS) wf_traverse_kernel(const WfParams p) {
+template <bool BRUTE, bool COUNT>
+__global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_traverse_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const unsigned int FULL = 0xffffffffu;
     const unsigned int n = *p.tn;
@@ -225,10 +219,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, WIDE ? RTB_TRAV4_MIN_BLOCKS
         // all 32 lanes enter together (lanes without a ray hold a finished state): while the queue has
         // rays, leave the tree when `refill` lanes are free; afterwards run to the end
         // (the quota counts finished lanes of the whole warp: the lanes that are free now, plus at least one)
-        if (!BRUTE) {
-            if (WIDE) trav_run<RTB_TRAV4_NODE_STEPS, true>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
-            else trav_run<2, false>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
-        }
+        if (!BRUTE) trav_run<2>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
 #endif
     }
     if (COUNT && p.counters) {
@@ -317,22 +308,17 @@ cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int block
 
 cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {
     if (brute) {
-        if (count) wf_traverse_kernel<true, true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<true, false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-    } else if (p.wide) {
-        if (count) wf_traverse_kernel<false, true, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<false, false, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        if (count) wf_traverse_kernel<true, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
     } else {
-        if (count) wf_traverse_kernel<false, true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<false, false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        if (count) wf_traverse_kernel<false, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
 
-cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm, int *traverse4_blocks_per_sm) {
+cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm) {
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false, false>, 256, 0);
     if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false, false>, RTB_BLOCK_THREADS, 0);
-    if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse4_blocks_per_sm, wf_traverse_kernel<false, false, true>, RTB_BLOCK_THREADS, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false>, RTB_BLOCK_THREADS, 0);
 }

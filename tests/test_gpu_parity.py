@@ -131,43 +131,6 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
         assert out[0][2][k] == out[1][2][k]
 
 
-@pytest.mark.parametrize("sid,p0,p1", SCENES + [(6, 12, 10)])
-def test_wide_nodes_equal_binary_nodes(tracer, sid, p0, p1):
-    """option bvh_width = 4: wf_traverse walks the 4-wide view of the same tree (rtb_lbvh.cu, collapse4_kernel).
-    A traversal order must never change a result: images, progressive frames and segment counters are
-    bit-identical to the binary walk's and to brute force, default and strict builds, both builders."""
-    scene = _scene(sid, p0, p1)
-    try:
-        for builder, strict in ((1, 0), (1, 1), (0, 0)):
-            tracer.set_option("builder", builder)
-            tracer.set_option("strict_fp", strict)
-            tracer.set_option("kernel", 1)
-            tracer.setup(scene, W, H, 3, 6)
-            out = []
-            for width, traversal in ((2, 0), (4, 0), (4, 1)):
-                if traversal == 1 and (builder, strict) != (1, 0):
-                    continue
-                tracer.set_option("bvh_width", width)
-                tracer.set_option("traversal", traversal)
-                tracer.set_option("counters", 1)
-                img = np.zeros((H, W, 3), np.float32)
-                f = tracer.render(img, 0, 4242)
-                c = tracer.counters()
-                tracer.set_option("counters", 0)
-                assert int(tracer.info("bvh_width")) == (width if int(tracer.info("num_nodes")) > 0 else 2)
-                f = tracer.render(img, f, 17)
-                out.append((img, c))
-            for img, c in out[1:]:
-                assert (img == out[0][0]).all(), f"builder {builder} strict {strict}"
-                for k in ("segments", "hit_segments", "samples"):
-                    assert c[k] == out[0][1][k]
-            if int(tracer.info("num_nodes")) > 64:
-                assert out[1][1]["box_tests"] != out[0][1]["box_tests"], "the 4-wide walk did not run"
-    finally:
-        for k, v in (("builder", 1), ("strict_fp", 0), ("kernel", 2), ("bvh_width", 0), ("traversal", 0), ("counters", 0)):
-            tracer.set_option(k, v)
-
-
 @pytest.mark.parametrize("groups,streams", [(2, 1), (3, 2), (7, 2)])
 def test_wavefront_row_groups_and_streams(tracer, groups, streams):
     """Row groups (L2 residency) and two concurrent streams only reorder the work: same bits."""
