@@ -126,7 +126,7 @@ def bytes_per_ray(c):
 
 def cpu_baseline_leg(workload, threads):
     """The reference's own source on the host cores (oracle/_ref), else the C port: a bounded band of
-    the same workload at 1 spp.  Returns the cpu_baseline object."""
+    the same workload at a few spp.  Returns the cpu_baseline object."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import ctypes
     import numpy as np
@@ -139,7 +139,8 @@ def cpu_baseline_leg(workload, threads):
     nb, band = 8, max(1, H // 128)
     bands = [((2 * b + 1) * H // (2 * nb) - band // 2, (2 * b + 1) * H // (2 * nb) - band // 2 + band) for b in range(nb)]
     scene = rtb.Scene(sid, p0, p1)
-    rd = scene.render_settings(1, bounces)
+    sample_spp = 4  # about 10 s of single-threaded CPU work on the C3 sample
+    rd = scene.render_settings(sample_spp, bounces)
     rays, dt = 0, 0.0
     if ob.have_ref_host():
         ref = ob.RefHost()
@@ -165,7 +166,7 @@ def cpu_baseline_leg(workload, threads):
             rays += cnt.segments
         kind = "port"
     return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
-            "sample": f"{workload} scene at {W}x{H}, {nb} bands of {band} rows spread over the frame, 1 spp, {bounces} bounces: {rays} rays in {dt:.2f} s"
+            "sample": f"{workload} scene at {W}x{H}, {nb} bands of {band} rows spread over the frame, {sample_spp} spp, {bounces} bounces: {rays} rays in {dt:.2f} s"
                       + (" (6x5 instance grid)" if sid == 6 else "")}
 
 
