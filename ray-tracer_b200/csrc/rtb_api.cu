@@ -391,7 +391,12 @@ int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num);
 // paths in a closed room favour the wavefront kernels, short paths or few pixels per GPU the
 // megakernel); the images are bit-identical either way.
 #define RTB_TUNE_SPP 8
+// the wavefront kernels pack the bounce index in 8 bits and the sample index in 24 (rtb_wavefront.cuh);
+// the reference has no such limits, so beyond them the automatic choice is the megakernel
+bool wavefront_fits(const rtb_ctx *c) { return c->rd.reflection_limit <= 255 && (long long)c->rd.rays_per_pixel < (1 << 24); }
+
 int autotune_kernel(rtb_ctx *c) {
+    if (!wavefront_fits(c)) { c->auto_choice = 0; return 0; }
     c->auto_choice = 1;
     if (c->opt_counters || c->image_floats == 0) return 0;  // counted builds are not timed
     float *scratch = nullptr;
@@ -435,7 +440,7 @@ int autotune_kernel(rtb_ctx *c) {
     return 0;
 }
 
-int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? 1 : c->auto_choice) : c->opt_kernel; }
+int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? (wavefront_fits(c) ? 1 : 0) : c->auto_choice) : c->opt_kernel; }
 
 int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     if (c->opt_kernel == 2 && c->auto_choice < 0 && autotune_kernel(c) != 0) return 1;
@@ -481,8 +486,9 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     int local_rows = shard_local_rows(c, c->shard_rank);
     size_t slots = (size_t)c->width * local_rows;
     if (slots == 0) return 0;
-    if (c->rd.reflection_limit > 255) return fail(c, "render", "the wavefront kernels pack the bounce index in 8 bits (reflection_limit <= 255)");
-    if ((long long)c->rd.rays_per_pixel >= (1 << 24)) return fail(c, "render", "the wavefront kernels pack the sample index in 24 bits");
+    if (!wavefront_fits(c))
+        return fail(c, "render", "the wavefront kernels pack the bounce index in 8 bits and the sample index in 24 (reflection_limit <= 255, rays_per_pixel < 2^24): "
+                                 "use option kernel = 0 or 2");
     if (c->wf_slots < slots) {
         if (c->d_wf_state) cudaFree(c->d_wf_state);
         if (c->d_wf_queue) cudaFree(c->d_wf_queue);

@@ -466,3 +466,27 @@ def test_edge_cases(tracer):
     # bad material index is refused
     assert lib.rtb_scene_add_sphere(tracer.ctx, c, 1.0, 99) < 0
     assert b"Error from CUDA" in lib.rtb_last_error(tracer.ctx)
+
+
+def test_bounce_limit_beyond_the_wavefront_packing(tracer):
+    """The reference has no upper bound on reflection_limit (src/raytracer.cu:72); the wavefront kernels pack the
+    bounce index in 8 bits.  With the automatic kernel choice (the default) a limit of 300 renders through the
+    megakernel, bit-identical to a pinned megakernel; pinning the wavefront kernels is refused with the
+    reference's error shape."""
+    scene = _scene(1, 0, 0)  # reflections: paths that use many bounces
+    imgs = {}
+    try:
+        for kernel in (2, 0):
+            tracer.set_option("kernel", kernel)
+            tracer.setup(scene, 64, 48, 2, 300)
+            img = np.zeros((48, 64, 3), np.float32)
+            assert tracer.render(img, 0, 7) == 1
+            assert int(tracer.info("kernel")) == 0
+            imgs[kernel] = img
+        assert (imgs[0] == imgs[2]).all() and np.isfinite(imgs[0]).all()
+        tracer.set_option("kernel", 1)
+        with pytest.raises(Exception, match="Error from CUDA"):
+            tracer.render(np.zeros((48, 64, 3), np.float32), 0, 7)
+    finally:
+        tracer.set_option("kernel", 2)
+        tracer.setup(scene, 64, 48, 1, 3)
