@@ -197,7 +197,10 @@ struct Flat {
             float4 a = tris[3 * (idx + k)], b = tris[3 * (idx + k) + 1], cc = tris[3 * (idx + k) + 2];
             float p[3][3] = {{a.x, a.y, a.z}, {a.x + a.w, a.y + b.x, a.z + b.y}, {a.x + b.z, a.y + b.w, a.z + cc.x}};
             for (int v = 0; v < 3; v++)
-                for (int c = 0; c < 3; c++) { blo[c] = fminf(blo[c], p[v][c]); bhi[c] = fmaxf(bhi[c], p[v][c]); }
+                for (int c = 0; c < 3; c++) {  // fminf / fmaxf written out: libm calls otherwise, 18 per triangle
+                    blo[c] = (blo[c] < p[v][c] || p[v][c] != p[v][c]) ? blo[c] : p[v][c];
+                    bhi[c] = (bhi[c] > p[v][c] || p[v][c] != p[v][c]) ? bhi[c] : p[v][c];
+                }
         }
     }
 
@@ -295,6 +298,12 @@ int flatten(rtb_ctx *c, Flat &f) {
                 if (o.tri_first < 0 || o.tri_count < 0 || (size_t)(o.tri_first + o.tri_count) * 9 > c->tri_points.size())
                     return fail(c, "flattening scene", "mesh triangle range out of bounds");
                 const float *pts = c->tri_points.data() + (size_t)o.tri_first * 9;
+                {   // one growth step per array instead of ~20 doublings for a million-triangle mesh
+                    size_t nt = f.tri_ids.size() + (size_t)o.tri_count;
+                    f.tris.reserve(3 * nt); f.tri_ids.reserve(nt); f.tri_uv.reserve(3 * nt); f.tri_refleaf.reserve(nt);
+                    f.leaf_refs.reserve(f.leaf_refs.size() + (size_t)o.tri_count); f.leaf_area.reserve(f.leaf_area.size() + (size_t)o.tri_count);
+                    f.leaf_box.reserve(f.leaf_box.size() + 6 * (size_t)o.tri_count);
+                }
                 RefBvh rb;
                 int node_base = (int)(f.ref_nodes.size() / 2);
                 if (c->opt_ref_quirks) {

@@ -15,9 +15,15 @@
 // box (:708-719) with a top-down merge sort that takes from the RIGHT run on ties (:655-706) and
 // the first n/2+1 go left (:641-650).  Everything is float arithmetic on the host: compile with
 // -ffp-contract=off.
+// The preorder node numbers of the reference's recursion follow from the triangle counts alone
+// (count_nodes), so the two subtrees of a node -- and the two halves of a merge sort -- are built by
+// separate threads near the root: the result is the serial one, a million-triangle mesh takes a
+// fraction of the time (the commit of a dynamic scene waits for this).
 #include "rtb_refbvh.h"
+#include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 namespace rtb {
 namespace {
@@ -27,23 +33,86 @@ struct Item {
     float dist;
 };
 
-void merge_sort(Item *a, int n, Item *tmp) {
+// glibc's fminf / fmaxf written out (the second argument on ties, the other one if an argument is NaN):
+// g++ calls libm for them unless -ffinite-math-only, and the box loops below run 18 of them per triangle
+inline float min_f(float x, float y) { return (x < y || y != y) ? x : y; }
+inline float max_f(float x, float y) { return (x > y || y != y) ? x : y; }
+
+// `par` = levels of the recursion that still fork a thread (0 = serial).  The two halves are disjoint
+// ranges of `a` and `tmp`, so the result does not depend on it.
+void merge_sort(Item *a, int n, Item *tmp, int par) {
     if (n <= 1) return;
     int nl = n / 2, nr = n - nl;
-    merge_sort(a, nl, tmp);
-    merge_sort(a + nl, nr, tmp);
-    int l = 0, r = 0;
-    for (int k = 0; k < n; k++) {
-        bool take_left;
-        if (l >= nl) take_left = false;
-        else if (r >= nr) take_left = true;
-        else take_left = a[l].dist < a[nl + r].dist;
-        tmp[k] = take_left ? a[l++] : a[nl + r++];
+    if (par > 0 && n >= 4096) {
+        std::thread left([=] { merge_sort(a, nl, tmp, par - 1); });
+        merge_sort(a + nl, nr, tmp + nl, par - 1);
+        left.join();
+    } else {
+        merge_sort(a, nl, tmp, 0);
+        merge_sort(a + nl, nr, tmp + nl, 0);
     }
+    // ties take from the RIGHT run (src/objects.cu:655-706).  The body has no data-dependent branch (the
+    // outcome of the comparison is a coin flip on real data): select, then advance one of the cursors.
+    const Item *b = a + nl;
+    int l = 0, r = 0, k = 0;
+    while (l < nl && r < nr) {
+        bool take_left = a[l].dist < b[r].dist;
+        tmp[k++] = take_left ? a[l] : b[r];
+        l += take_left;
+        r += !take_left;
+    }
+    if (l < nl) std::memcpy(tmp + k, a + l, sizeof(Item) * (nl - l));
+    else std::memcpy(tmp + k, b + r, sizeof(Item) * (nr - r));
     std::memcpy(a, tmp, sizeof(Item) * n);
 }
 
-int build(const float *pts, Item *items, int n, int depth, Item *tmp, RefBvh &out) {
+// The merge sort above orders by (dist ascending, position in the input DESCENDING): a merge that takes
+// from the right run on ties puts equal keys in reverse input order, at every level of the recursion.
+// That is a total order when no dist is NaN, so any sort that realises it gives the same array: here a
+// stable LSD radix sort (3 passes of 11 bits over the float's bit pattern -- dist is a square root, never
+// negative, so the patterns order like the values) of the REVERSED input.  Linear time instead of
+// n log n unpredictable branches: the sorts were three quarters of the partition's time.
+void sort_items(Item *a, int n, Item *tmp, int par) {
+    bool ordered_bits = true;
+    for (int i = 0; i < n; i++) ordered_bits &= a[i].dist >= 0.f;  // false for NaN (and for a negative value, which sqrtf never returns)
+    if (n < 2048 || !ordered_bits) {
+        merge_sort(a, n, tmp, par);
+        return;
+    }
+    std::reverse(a, a + n);
+    std::vector<unsigned int> hist(3 * 2048, 0u);
+    auto bits = [](const Item &it) { unsigned int u; std::memcpy(&u, &it.dist, 4); return u; };
+    for (int i = 0; i < n; i++) {
+        unsigned int u = bits(a[i]);
+        hist[u & 2047u]++; hist[2048 + ((u >> 11) & 2047u)]++; hist[4096 + (u >> 22)]++;
+    }
+    for (int pass = 0; pass < 3; pass++) {
+        unsigned int *h = hist.data() + 2048 * pass, sum = 0;
+        for (int d = 0; d < 2048; d++) { unsigned int c = h[d]; h[d] = sum; sum += c; }
+    }
+    Item *src = a, *dst = tmp;
+    for (int pass = 0; pass < 3; pass++) {
+        unsigned int *h = hist.data() + 2048 * pass;
+        const int shift = 11 * pass;
+        for (int i = 0; i < n; i++) dst[h[(bits(src[i]) >> shift) & 2047u]++] = src[i];
+        Item *t = src; src = dst; dst = t;
+    }
+    std::memcpy(a, tmp, sizeof(Item) * n);  // three passes: the result is in tmp
+}
+
+int left_count(int n) { return n / 2 + 1 > n ? n : n / 2 + 1; }  // src/objects.cu:641-650
+
+// nodes of the subtree over n triangles with `depth` levels below it: the preorder numbering of the
+// reference's recursive build, known before the build runs, so subtrees can be built concurrently
+int count_nodes(int n, int depth) {
+    if (n == 0) return 0;
+    if (depth <= 0) return 1;
+    int nl = left_count(n);
+    return 1 + count_nodes(nl, depth - 1) + count_nodes(n - nl, depth - 1);
+}
+
+// builds the subtree whose root is node `me` (nodes are pre-sized); returns me, or -1 for an empty range
+int build(const float *pts, Item *items, int n, int depth, Item *tmp, RefBvh &out, int me, int par) {
     if (n == 0) return -1;  // the reference makes an empty (0,0,0) box here: degenerate, never hit, holds nothing
     RefBvhNode node;
     for (int c = 0; c < 3; c++) node.lo[c] = node.hi[c] = pts[9 * (size_t)items[0].tri + c];
@@ -51,13 +120,12 @@ int build(const float *pts, Item *items, int n, int depth, Item *tmp, RefBvh &ou
         const float *p = pts + 9 * (size_t)items[i].tri;
         for (int v = 0; v < 3; v++)
             for (int c = 0; c < 3; c++) {
-                node.lo[c] = fminf(node.lo[c], p[3 * v + c]);
-                node.hi[c] = fmaxf(node.hi[c], p[3 * v + c]);
+                node.lo[c] = min_f(node.lo[c], p[3 * v + c]);
+                node.hi[c] = max_f(node.hi[c], p[3 * v + c]);
             }
     }
     node.parent = -1;
-    int me = (int)out.nodes.size();
-    out.nodes.push_back(node);
+    out.nodes[me] = node;
     if (depth <= 0) {
         bool flat = node.lo[0] == node.hi[0] || node.lo[1] == node.hi[1] || node.lo[2] == node.hi[2];
         for (int i = 0; i < n; i++) {
@@ -77,11 +145,18 @@ int build(const float *pts, Item *items, int n, int depth, Item *tmp, RefBvh &ou
         float mag_sq = x * x + y * y + z * z;
         items[i].dist = sqrtf(mag_sq);
     }
-    merge_sort(items, n, tmp);
-    int n_left = n / 2 + 1;
-    if (n_left > n) n_left = n;
-    int l = build(pts, items, n_left, depth - 1, tmp, out);
-    int r = build(pts, items + n_left, n - n_left, depth - 1, tmp, out);
+    sort_items(items, n, tmp, par);
+    int n_left = left_count(n);
+    int left_root = me + 1, right_root = me + 1 + count_nodes(n_left, depth - 1);
+    int l, r;
+    if (par > 0 && n >= 4096) {
+        std::thread left([&] { l = build(pts, items, n_left, depth - 1, tmp, out, left_root, par - 1); });
+        r = build(pts, items + n_left, n - n_left, depth - 1, tmp + n_left, out, right_root, par - 1);
+        left.join();
+    } else {
+        l = build(pts, items, n_left, depth - 1, tmp, out, left_root, 0);
+        r = build(pts, items + n_left, n - n_left, depth - 1, tmp + n_left, out, right_root, 0);
+    }
     if (l >= 0) out.nodes[l].parent = me;
     if (r >= 0) out.nodes[r].parent = me;
     return me;
@@ -89,14 +164,18 @@ int build(const float *pts, Item *items, int n, int depth, Item *tmp, RefBvh &ou
 
 }  // namespace
 
-void ref_bvh_partition(const float *points, int n, RefBvh &out) {
+void ref_bvh_partition(const float *points, int n, RefBvh &out, int threads) {
     out.nodes.clear();
     out.leaf_of.assign(n > 0 ? n : 0, -1);
     out.degenerate.assign(n > 0 ? n : 0, 0);
     if (n <= 0) return;
     std::vector<Item> items(n), tmp(n);
     for (int i = 0; i < n; i++) items[i] = Item{i, 0.f};
-    build(points, items.data(), n, 10, tmp.data(), out);
+    if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+    int par = 0;  // fork levels: 2^par concurrent subtrees / sort runs
+    while (par < 5 && (2 << par) <= threads) par++;
+    out.nodes.resize(count_nodes(n, 10));
+    build(points, items.data(), n, 10, tmp.data(), out, 0, par);
 }
 
 }  // namespace rtb

@@ -17,7 +17,9 @@ struct RefBvh {
     std::vector<char> degenerate;  // per mesh triangle: 1 if its leaf box has zero extent on an axis
 };
 
-// points: 9 floats per triangle (p0 p1 p2), n triangles of ONE mesh object
-void ref_bvh_partition(const float *points, int n, RefBvh &out);
+// points: 9 floats per triangle (p0 p1 p2), n triangles of ONE mesh object.
+// threads: host threads near the root of the recursion (1 = serial, 0 = all hardware threads); the
+// result does not depend on it.
+void ref_bvh_partition(const float *points, int n, RefBvh &out, int threads = 0);
 
 }  // namespace rtb

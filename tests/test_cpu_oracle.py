@@ -244,6 +244,21 @@ def test_rng_fma_conversion_is_exact_for_all_inputs(tmp_path):
     assert "float_mismatches 0 " in r.stdout
 
 
+# ---------------------------------------------------------------- host logic: the reference-BVH partition
+def test_reference_bvh_partition_fast_path_equals_literal_restatement(tmp_path):
+    """rtb_refbvh.cpp finds the reference's degenerate leaves with a radix sort and host threads;
+    tests/refbvh_check.cpp holds the literal recursion (merge sort, ties from the right run) and compares
+    nodes, parents, leaf assignment and degenerate flags bit for bit, 1 / 2 / all threads."""
+    here = os.path.dirname(os.path.abspath(__file__))
+    csrc = os.path.join(os.path.dirname(here), "ray-tracer_b200", "csrc")
+    exe = tmp_path / "refbvh_check"
+    subprocess.run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-I", csrc, "-o", str(exe), os.path.join(here, "refbvh_check.cpp"),
+                    os.path.join(csrc, "rtb_refbvh.cpp"), "-lpthread"], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "mismatches 0" in r.stdout
+
+
 # ---------------------------------------------------------------- the C-ABI library without a GPU
 def test_library_exports_every_declared_symbol():
     names = rtb.declared_symbols()
