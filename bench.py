@@ -170,6 +170,27 @@ def cpu_baseline_leg(workload, threads):
                       + (" (6x5 instance grid)" if sid == 6 else "")}
 
 
+def ncu_traffic(workload, kernel_kind):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the two wavefront kernels, from the committed
+    `ncu --set full` summaries (profiles/r1e_ncu_*_C3.txt: launch 46 of a 4-spp C3 run); None for other workloads."""
+    if workload != "C3" or kernel_kind != 1:
+        return None
+    out = {}
+    for kern in ("wf_traverse", "wf_shade"):
+        path = os.path.join(ROOT, "profiles", f"r1e_ncu_{kern}_C3.txt")
+        if not os.path.exists(path):
+            return None
+        total = 0.0
+        for ln in open(path):
+            if ln.startswith(("dram__bytes_read.sum,", "dram__bytes_write.sum,")):
+                val, unit = ln.split(",", 1)[1].split()[:2]
+                total += float(val) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+        out[kern + "_kernel"] = total
+    out["unit"] = "bytes per launch"
+    out["source"] = "profiles/r1e_ncu_wf_traverse_C3.txt, profiles/r1e_ncu_wf_shade_C3.txt (ncu --set full, launch 46 of a 4-spp C3 frame: ~2 M live pixels)"
+    return out
+
+
 def reference_arm(args):
     """--impl reference.  Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
@@ -429,7 +450,7 @@ def main():
             "roofline": {"bound": "fp32", "kernel": "wf_traverse_kernel + wf_shade_kernel (all launches of a step)" if kernel_kind == 1 else "render_megakernel",
                          "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak if fp32_peak else None,
                          "peak_kind": "measured FFMA microbenchmark on this GPU (rtb_measure_fp32_peak)", "peak_nominal": nominal_peak,
-                         "frac_of_nominal": achieved_tf / nominal_peak, "traffic": None,
+                         "frac_of_nominal": achieved_tf / nominal_peak, "traffic": ncu_traffic(args.workload, kernel_kind),
                          "flops_per_ray": fpr, "kernel_ms": kernel_ms,
                          "op_mix_per_ray": {"box": cnt["box_tests"] / cnt["segments"], "tri": cnt["tri_tests"] / cnt["segments"],
                                             "sphere": cnt["sphere_tests"] / cnt["segments"], "hit": cnt["hit_segments"] / cnt["segments"]},

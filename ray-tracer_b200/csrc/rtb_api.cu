@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <chrono>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -212,6 +213,20 @@ struct Flat {
         tri_refleaf.push_back(refleaf);
         return idx;
     }
+    // the same records as add_tri, written at known positions of pre-sized arrays (triangle `idx`, leaf
+    // `leaf_pos`), so that the triangles of a big mesh can be flattened by several host threads; the box goes
+    // into blo / bhi for the caller's own bounds
+    void set_tri(size_t idx, size_t leaf_pos, TriRec t, int obj, int sub, const float *uv, int refleaf, float *blo, float *bhi) {
+        tris[3 * idx] = t.a; tris[3 * idx + 1] = t.b; tris[3 * idx + 2] = t.c;
+        tri_ids[idx] = make_int2(obj, sub);
+        for (int k = 0; k < 3; k++) tri_uv[3 * idx + k] = uv ? make_float2(uv[2 * k], uv[2 * k + 1]) : make_float2(0, 0);
+        tri_refleaf[idx] = refleaf;
+        leaf_refs[leaf_pos] = ~(((int)idx << RTB_KIND_BITS) | KIND_TRI);
+        tri_box((int)idx, 1, blo, bhi);
+        float e[3] = {bhi[0] - blo[0], bhi[1] - blo[1], bhi[2] - blo[2]};
+        leaf_area[leaf_pos] = 2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
+        for (int c = 0; c < 3; c++) { leaf_box[6 * leaf_pos + c] = blo[c]; leaf_box[6 * leaf_pos + 3 + c] = bhi[c]; }
+    }
     void add_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
         int idx = push_tri(t, obj, sub, uv, refleaf);
         leaf_refs.push_back(~((idx << RTB_KIND_BITS) | KIND_TRI));
@@ -298,12 +313,6 @@ int flatten(rtb_ctx *c, Flat &f) {
                 if (o.tri_first < 0 || o.tri_count < 0 || (size_t)(o.tri_first + o.tri_count) * 9 > c->tri_points.size())
                     return fail(c, "flattening scene", "mesh triangle range out of bounds");
                 const float *pts = c->tri_points.data() + (size_t)o.tri_first * 9;
-                {   // one growth step per array instead of ~20 doublings for a million-triangle mesh
-                    size_t nt = f.tri_ids.size() + (size_t)o.tri_count;
-                    f.tris.reserve(3 * nt); f.tri_ids.reserve(nt); f.tri_uv.reserve(3 * nt); f.tri_refleaf.reserve(nt);
-                    f.leaf_refs.reserve(f.leaf_refs.size() + (size_t)o.tri_count); f.leaf_area.reserve(f.leaf_area.size() + (size_t)o.tri_count);
-                    f.leaf_box.reserve(f.leaf_box.size() + 6 * (size_t)o.tri_count);
-                }
                 RefBvh rb;
                 int node_base = (int)(f.ref_nodes.size() / 2);
                 if (c->opt_ref_quirks) {
@@ -316,13 +325,45 @@ int flatten(rtb_ctx *c, Flat &f) {
                         f.ref_nodes.push_back(make_float4(n.hi[0], n.hi[1], n.hi[2], 0.f));
                     }
                 }
-                for (int k = 0; k < o.tri_count; k++) {
-                    if (c->opt_ref_quirks && rb.degenerate[k]) { f.culled++; continue; }  // invisible in the reference
-                    const float *p = pts + (size_t)k * 9;
-                    const float *uv = c->tri_uv.empty() ? nullptr : c->tri_uv.data() + (size_t)(o.tri_first + k) * 6;
-                    f.add_tri(make_tri(H3{p[0], p[1], p[2]}, H3{p[3], p[4], p[5]}, H3{p[6], p[7], p[8]}), i, k, uv,
-                              c->opt_ref_quirks ? node_base + rb.leaf_of[k] : -1);
+                // kept triangles get consecutive positions (degenerate leaves are invisible in the reference and
+                // dropped), then the records are written in place, by several host threads for a big mesh
+                std::vector<int> slot((size_t)o.tri_count);
+                int kept = 0;
+                for (int k = 0; k < o.tri_count; k++) slot[k] = (c->opt_ref_quirks && rb.degenerate[k]) ? -1 : kept++;
+                f.culled += o.tri_count - kept;
+                const size_t tri_base = f.tri_ids.size(), leaf_base = f.leaf_refs.size();
+                f.tris.resize(3 * (tri_base + kept)); f.tri_ids.resize(tri_base + kept); f.tri_uv.resize(3 * (tri_base + kept));
+                f.tri_refleaf.resize(tri_base + kept);
+                f.leaf_refs.resize(leaf_base + kept); f.leaf_area.resize(leaf_base + kept); f.leaf_box.resize(6 * (leaf_base + kept));
+                int workers = o.tri_count >= 32768 ? (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+                std::vector<float> wlo((size_t)workers * 3, 3e38f), whi((size_t)workers * 3, -3e38f);
+                auto fill = [&](int w) {
+                    int k0 = (int)((long long)o.tri_count * w / workers), k1 = (int)((long long)o.tri_count * (w + 1) / workers);
+                    for (int k = k0; k < k1; k++) {
+                        if (slot[k] < 0) continue;
+                        const float *p = pts + (size_t)k * 9;
+                        const float *uv = c->tri_uv.empty() ? nullptr : c->tri_uv.data() + (size_t)(o.tri_first + k) * 6;
+                        float blo[3], bhi[3];
+                        f.set_tri(tri_base + slot[k], leaf_base + slot[k], make_tri(H3{p[0], p[1], p[2]}, H3{p[3], p[4], p[5]}, H3{p[6], p[7], p[8]}), i, k, uv,
+                                  c->opt_ref_quirks ? node_base + rb.leaf_of[k] : -1, blo, bhi);
+                        for (int a = 0; a < 3; a++) {
+                            if (blo[a] < wlo[3 * w + a]) wlo[3 * w + a] = blo[a];
+                            if (bhi[a] > whi[3 * w + a]) whi[3 * w + a] = bhi[a];
+                        }
+                    }
+                };
+                if (workers == 1) {
+                    fill(0);
+                } else {
+                    std::vector<std::thread> pool;
+                    for (int w = 0; w < workers; w++) pool.emplace_back(fill, w);
+                    for (std::thread &t : pool) t.join();
                 }
+                for (int w = 0; w < workers; w++)
+                    for (int a = 0; a < 3; a++) {
+                        if (wlo[3 * w + a] < f.lo[a]) f.lo[a] = wlo[3 * w + a];
+                        if (whi[3 * w + a] > f.hi[a]) f.hi[a] = whi[3 * w + a];
+                    }
                 break;
             }
             default: return fail(c, "flattening scene", "unknown object type");

@@ -490,3 +490,30 @@ def test_bounce_limit_beyond_the_wavefront_packing(tracer):
     finally:
         tracer.set_option("kernel", 2)
         tracer.setup(scene, 64, 48, 1, 3)
+
+
+def test_big_mesh_flattened_by_host_threads(tracer):
+    """A mesh of 72 300 triangles (10 x 10 monkeys) takes the threaded paths of the host flatten (rtb_api.cu)
+    and of the reference-BVH partition (rtb_refbvh.cpp): strict ids / distances equal the oracle's bit for bit
+    and the tree render equals brute force over the primitives."""
+    scene = _scene(6, 10, 10)
+    w, h = 96, 64
+    try:
+        tracer.set_option("strict_fp", 1)
+        tracer.setup(scene, w, h, 1, 2)
+        assert int(tracer.info("num_prims")) > 32768
+        obj, sub, t = tracer.primary_ids()
+        o_obj, o_sub, o_t = ob.Oracle(scene).primary_ids(rtb.default_camera(w, h), w, h)
+        assert (obj == o_obj).all() and (sub == o_sub).all() and (t == o_t).all()
+        assert (obj >= 0).mean() > 0.3
+        tracer.set_option("strict_fp", 0)
+        imgs = []
+        for trav in (0, 1):
+            tracer.set_option("traversal", trav)
+            img = np.zeros((h, w, 3), np.float32)
+            tracer.render(img, 0, 4242)
+            imgs.append(img)
+        assert (imgs[0] == imgs[1]).all()
+    finally:
+        tracer.set_option("strict_fp", 0)
+        tracer.set_option("traversal", 0)
