@@ -219,7 +219,13 @@ int rtb_primary_ids(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
 /* counters of the last render when option "counters" = 1 */
 int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
 /* options: "counters" 0/1; "traversal" 0 = LBVH, 1 = brute force over the flattened primitives;
- * "kernel" 0 = persistent megakernel, 1 = wavefront; "block_threads"; "blocks_per_sm" */
+ * "kernel" 0 = persistent megakernel, 1 = wavefront, 2 = timed choice between the two at the first frame
+ * (default; bit-identical images; beyond the wavefront kernels' packing limits -- reflection_limit > 255 or
+ * rays_per_pixel >= 2^24 -- the choice is the megakernel, while "kernel" = 1 refuses such a frame);
+ * "strict_fp" 0/1 (kernels built with -fmad=false); "builder" 0 = Karras LBVH, 1 = PLOC (next commit);
+ * "large_split", "max_large", "reference_bvh_quirks" (next commit); "walk_min", "refill", "wf_refill",
+ * "wf_rebuild", "wf_groups", "wf_streams" (traversal / wavefront policy, 0 = tuned); "block_threads";
+ * "blocks_per_sm".  Every change re-arms the timed choice. */
 int rtb_set_option(rtb_ctx *ctx, const char *key, int value);
 int rtb_get_info(rtb_ctx *ctx, const char *key, double *value);
 /* sustained FP32 FMA throughput of the device (TFLOP/s, dependent-chain FFMA microbenchmark over
