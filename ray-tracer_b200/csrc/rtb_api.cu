@@ -74,12 +74,6 @@ struct rtb_ctx {
     // option "wf_timing": CUDA events around every launch of the next frame (diagnostics only)
     int opt_wf_timing = 0;
     int opt_wf_rebuild = 16;  // iterations between queue rebuilds (0 = never)
-    // option "wf_carry": NODE iterations a traversal warp may spend once the queue is empty before it parks its
-    // unfinished rays for the next iteration (rtb_wavefront.cuh); 0 = off (every launch runs its longest ray out)
-    int opt_wf_carry = 0, opt_wf_carry_cap = 65536;
-    int *d_wf_carry = nullptr;
-    size_t wf_carry_cap = 0;
-    int last_extra_iterations = 0;
     int opt_wf_groups = 2, opt_wf_streams = 2;  // row groups taken through the frame one after the other / concurrent groups
     cudaStream_t stream2 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -581,21 +575,6 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     base.walk_min = c->opt_walk_min < 1 ? c->tuned_wf_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     base.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
-    const bool carry = c->opt_wf_carry > 0 && !brute && c->opt_wf_timing == 0;
-    c->last_extra_iterations = 0;
-    base.carry_in = nullptr; base.carry_out = nullptr; base.carry_n_in = nullptr; base.carry_n_out = nullptr; base.carry_zero = nullptr;
-    base.carry_cap = 0; base.carry_budget = 0;
-    if (carry) {
-        size_t cap = (size_t)std::max(1024, c->opt_wf_carry_cap);
-        if (c->wf_carry_cap != cap) {
-            if (c->d_wf_carry) cudaFree(c->d_wf_carry);
-            c->d_wf_carry = nullptr; c->wf_carry_cap = 0;
-            RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_carry, 4 * cap * RTB_WF_CARRY_INTS * sizeof(int)), "allocating parked-ray records");
-            c->wf_carry_cap = cap;
-        }
-        base.carry_cap = (int)cap;
-        base.carry_budget = c->opt_wf_carry;
-    }
     int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
     const int trav_blocks = c->num_sms * trav_per_sm;
     const long long iterations = (long long)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
@@ -632,8 +611,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     struct Group {
         WfParams p;
         int *queue[2];
-        unsigned int *count[2], *tcount[2], *carry_n[2];
-        int *carry[2];
+        unsigned int *count[2], *tcount[2];
         int *block_count;
         size_t slot_base, slot_count;
         int shade_blocks;
@@ -644,9 +622,6 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
         g.p.queue_in = g.queue[in]; g.p.n_in = g.count[in];
         g.p.queue_out = g.queue[out]; g.p.n_out = g.count[out];
         g.p.tn = g.tcount[first ? 0 : out];  // the traversal queue of iteration k is counted in tcount[k & 1]
-        // traversal launch k reads the parked rays counted in carry_n[k & 1] and parks into carry_n[(k & 1) ^ 1]; the
-        // shade launch that follows it clears the counter it has consumed, for the launch after the next
-        g.p.carry_zero = (carry && !first) ? g.carry_n[in] : nullptr;
         return strict_fp ? strict::launch_wf_shade(g.p, brute, count_ops, g.shade_blocks, g.st) : fast::launch_wf_shade(g.p, brute, count_ops, g.shade_blocks, g.st);
     };
     cudaError_t e = cudaSuccess;
@@ -668,9 +643,6 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
             g.p.tqueue = c->d_wf_queue + 2 * slots + g.slot_base;
             unsigned int *cnt = c->d_wf_counts + 8 * l;
             g.count[0] = cnt; g.count[1] = cnt + 1; g.p.fetch = cnt + 2; g.tcount[0] = cnt + 4; g.tcount[1] = cnt + 5;
-            g.carry_n[0] = cnt + 6; g.carry_n[1] = cnt + 7;
-            g.carry[0] = carry ? c->d_wf_carry + (size_t)(2 * l) * c->wf_carry_cap * RTB_WF_CARRY_INTS : nullptr;
-            g.carry[1] = carry ? c->d_wf_carry + (size_t)(2 * l + 1) * c->wf_carry_cap * RTB_WF_CARRY_INTS : nullptr;
             g.block_count = c->d_wf_block_count + l * (((slots + 255) / 256) + 2);
             g.shade_blocks = (int)std::min<size_t>((g.slot_count + 255) / 256, (size_t)c->num_sms * c->wf_shade_per_sm);
             e = cudaMemsetAsync(cnt, 0, 8 * sizeof(unsigned int), g.st);
@@ -678,7 +650,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
             active++;
         }
         mark();
-        auto run_iteration = [&](long long k) {
+        for (long long k = 0; k < iterations && e == cudaSuccess; k++) {
             int in = (int)(k & 1), out = in ^ 1;
             for (int l = 0; l < active && e == cudaSuccess; l++) {
                 Group &g = gr[l];
@@ -691,29 +663,11 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
                 g.p.queue_in = g.queue[in]; g.p.n_in = g.count[in];
                 g.p.queue_out = g.queue[out]; g.p.n_out = g.count[out];
                 g.p.tn = g.tcount[in]; g.p.tn_next = g.tcount[out];
-                g.p.carry_in = g.carry[in]; g.p.carry_n_in = g.carry_n[in];
-                g.p.carry_out = g.carry[out]; g.p.carry_n_out = g.carry_n[out];
                 e = strict_fp ? strict::launch_wf_traverse(g.p, brute, count_ops, trav_blocks, g.st) : fast::launch_wf_traverse(g.p, brute, count_ops, trav_blocks, g.st);
                 mark();
                 if (e == cudaSuccess) e = launch_shade(g, 0, in, out);
                 mark();
             }
-        };
-        long long k = 0;
-        for (; k < iterations && e == cudaSuccess; k++) run_iteration(k);
-        // parked rays delay their pixels: run on, a few iterations at a time, until no pixel of these groups is live
-        // (the live count of queue[k & 1] is what the last wf_shade appended)
-        while (carry && e == cudaSuccess && k < 4 * iterations + 64) {
-            unsigned int live = 0;
-            for (int l = 0; l < active && e == cudaSuccess; l++) {
-                unsigned int n = 0;
-                e = cudaMemcpyAsync(&n, gr[l].count[k & 1], sizeof(unsigned int), cudaMemcpyDeviceToHost, gr[l].st);
-                if (e == cudaSuccess) e = cudaStreamSynchronize(gr[l].st);
-                live += n;
-            }
-            if (live == 0 || e != cudaSuccess) break;
-            for (int x = 0; x < 4 && e == cudaSuccess; x++, k++) run_iteration(k);
-            c->last_extra_iterations = (int)(k - iterations);
         }
     }
     if (lanes == 2 && e == cudaSuccess) {
@@ -825,7 +779,6 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->d_wf_counts) cudaFree(c->d_wf_counts);
     if (c->d_wf_alive) cudaFree(c->d_wf_alive);
     if (c->d_wf_block_count) cudaFree(c->d_wf_block_count);
-    if (c->d_wf_carry) cudaFree(c->d_wf_carry);
     for (cudaEvent_t ev : c->wf_events) cudaEventDestroy(ev);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
@@ -1321,8 +1274,6 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "wf_groups") c->opt_wf_groups = value < 1 ? 1 : value;
     else if (k == "wf_streams") c->opt_wf_streams = value < 1 ? 1 : value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
-    else if (k == "wf_carry") c->opt_wf_carry = value < 0 ? 0 : value;  // NODE iterations after the queue is empty before a warp parks its rays (0 = off)
-    else if (k == "wf_carry_cap") c->opt_wf_carry_cap = value;
     else if (k == "kernel") {
         if (value < 0 || value > 2) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice)");
         c->opt_kernel = value;
@@ -1374,8 +1325,6 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "kernel") *value = effective_kernel(c);      // the variant frames are rendered with
     else if (k == "kernel_option") *value = c->opt_kernel;     // 0, 1 or 2 = auto
     else if (k == "kernel_tuned") *value = c->opt_kernel == 2 && c->auto_choice >= 0 ? 1 : 0;
-    else if (k == "wf_carry") *value = c->opt_wf_carry;
-    else if (k == "wf_extra_iterations") *value = c->last_extra_iterations;
     else if (k == "tune_megakernel_ms") *value = c->tune_ms[0];
     else if (k == "tune_wavefront_ms") *value = c->tune_ms[1];
     else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) == 1 ? c->tuned_wf_walk_min : 8);

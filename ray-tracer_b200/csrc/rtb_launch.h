@@ -56,18 +56,8 @@ struct WfParams {
     unsigned int *tn, *tn_next; // its length (wf_shade appends, wf_traverse reads) / the counter wf_traverse zeroes for the next wf_shade
     int first;                  // wf_shade: 1 = no hit to consume yet (start of the frame)
     int refill, walk_min;
-    // option wf_carry (rtb_wavefront.cuh): parked rays of the previous / this traversal launch
-    const int *carry_in;
-    int *carry_out;
-    const unsigned int *carry_n_in;
-    unsigned int *carry_n_out;
-    unsigned int *carry_zero;   // wf_shade: the counter to clear for the traversal launch after the next one (nullptr = none)
-    int carry_cap;              // records per array; 0 = option off
-    int carry_budget;           // NODE iterations a warp may spend after the queue is empty
     unsigned long long *counters;
 };
-
-#define RTB_WF_CARRY_INTS 112  // ints per parked-ray record: 16 of header + the traversal stack (RTB_STACK = 96)
 
 struct LaunchConfig {
     int blocks, threads;

@@ -320,13 +320,10 @@ __device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &
 // quota: leave once this many lanes of the WARP hold a finished (or no) ray; <= 0 = run to completion.
 // NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
 // traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
-// BUDGET: the call also returns after `budget` iterations of the NODE phase (warp-uniform), whatever state
-// the rays are in -- the state is resumable, so the caller may park the unfinished rays (wf_traverse's tail).
-template <int NODE_STEPS = 1, bool BUDGET = false>
+template <int NODE_STEPS = 1>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
-                                         Counters &cnt, int budget = 0) {
+                                         Counters &cnt) {
     (void)mask;
-    bool spent = false;
     int cur = T.cur, leaf = T.leaf, sp = T.sp, top = T.top;
     Best best = T.best;
     // every round retires at least one node step or one leaf of some lane; the cap only turns a
@@ -341,7 +338,6 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
             finished = RTB_TRAV_MASK & ~walking & empty;
             if (!walking) break;
             if (__popc(walking) < walk_min && ((RTB_TRAV_MASK & ~empty) || (quota > 0 && __popc(finished) >= quota))) break;
-            if (BUDGET && budget-- <= 0) { spent = true; break; }
             RTB_COUNT(cnt, node_iters); RTB_COUNT_N(cnt, node_lanes, __popc(walking)); RTB_COUNT_N(cnt, node_blocked, __popc(RTB_TRAV_MASK & ~walking & ~empty));
             RTB_COUNT_N(cnt, node_done, __popc(finished)); RTB_COUNT_N(cnt, mask_lanes, __popc(RTB_TRAV_MASK));
 #pragma unroll
@@ -386,7 +382,6 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
         }
         unsigned alive = __ballot_sync(RTB_TRAV_MASK, cur != RTB_DONE || leaf < 0);
         if (!alive) break;
-        if (BUDGET && spent) break;
         if (quota > 0 && __popc(RTB_TRAV_MASK & ~alive) >= quota) break;
     }
     T.cur = cur; T.leaf = leaf; T.sp = sp; T.top = top; T.best = best;

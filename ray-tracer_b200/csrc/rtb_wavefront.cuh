@@ -23,8 +23,6 @@
 //   A {thr.xyz, cur_n}   B {col.xyz, rng bits}   C {acc.xyz, sample << 8 | bounce}
 //   O {origin.xyz, first node below the root}   D {direction.xyz, second node}   H {t, u, v, code}
 
-constexpr int WF_PENDING = -2;  // H.code of a pixel whose ray is parked (codes are >= 0, -1 = no hit)
-
 #ifndef RTB_SHADE_MIN_BLOCKS
 #define RTB_SHADE_MIN_BLOCKS 4
 #endif
@@ -47,14 +45,11 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
     unsigned long long n_seg = 0, n_hit = 0, n_samples = 0;
     Counters cnt;
     cnt = Counters{};
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        *p.fetch = 0;  // for the traversal launch that follows
-        if (p.carry_zero) *p.carry_zero = 0;  // the parked-ray counter the traversal launch AFTER that one appends to
-    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.fetch = 0;  // for the traversal launch that follows
     // whole warps walk the queue so that the ballot compaction below is converged
     for (unsigned int base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
         unsigned int i = base + lane;
-        bool live = i < n, pending = false;
+        bool live = i < n;
         int slot = 0;
         Ray ray;
         ray.o = f.cam_o; ray.d = v3(0, 0, 1); ray.inv = ray.d;
@@ -82,16 +77,11 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
                 ray.inv = ray.d;  // never read here: every direction change recomputes it (ray.cu:198-202)
                 Best best;
                 best.t = h.x; best.u = h.y; best.v = h.z; best.code = __float_as_int(h.w);
-                // the pixel's ray was parked by wf_traverse (option wf_carry) and is not finished: the pixel
-                // sits this iteration out -- nothing of its record changes, it stays in the queue
-                pending = best.code == WF_PENDING;
-                if (!pending) {
-                    bool hit = path_shade(s, f, ray, best, P);
-                    if (COUNT) { n_seg++; n_hit += hit; }
-                }
+                bool hit = path_shade(s, f, ray, best, P);
+                if (COUNT) { n_seg++; n_hit += hit; }
             }
             // advance until the pixel holds a ray to trace, or is finished
-            for (; !pending;) {
+            for (;;) {
                 if (P.bounce == 0) {
                     if (P.sample >= f.spp) {
                         path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
@@ -105,7 +95,7 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
                 }
                 break;
             }
-            if (live && !pending) {
+            if (live) {
                 ray_finalise(ray, f.aa, P.rng);  // antialias jitter, direction_inv
                 p.st.A[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, P.cur_n);
                 p.st.B[slot] = make_float4(P.col.x, P.col.y, P.col.z, __uint_as_float(P.rng));
@@ -117,16 +107,15 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
         // ... and take the root's node step (the root node sits in the kernel parameters): a ray
         // that cannot touch the tree closer than its large-primitive hit never enters wf_traverse
         unsigned int alive = __ballot_sync(0xffffffffu, live);
-        unsigned int fresh_rays = __ballot_sync(0xffffffffu, live && !pending);
         bool enter = false;
-        if (live && !pending) {
+        if (live) {
             Best first;
             int start = RTB_DONE, then = 0;
             if (BRUTE) {
                 first.t = RTB_INF_F; first.u = 0; first.v = 0; first.code = -1;
                 enter = true;
             } else {
-                large_prims_best(s, ray, first, fresh_rays, cnt);
+                large_prims_best(s, ray, first, alive, cnt);
                 root_step(s, ray, first, start, then, cnt);
                 enter = start != RTB_DONE;
             }
@@ -157,25 +146,11 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
 
 // Persistent traversal: every lane owns one ray at a time; finished lanes store their hit and
 // fetch the next ray as soon as `refill` of them are waiting (or nobody traverses any more).
-// CARRY (option wf_carry): every iteration of the wavefront loop ends with the longest ray of the launch -- a few
-// hundred dependent node fetches one lane at a time, which nothing else can hide once a rank's share of the
-// frame is small.  With CARRY a warp that finds the queue empty spends at most `carry_budget`
-// more NODE iterations on its rays and then PARKS the unfinished ones: slot, cursor, postponed leaf, best hit
-// and stack go to a record of `carry_out`, the pixel's H record is marked WF_PENDING (wf_shade then leaves
-// the pixel alone for an iteration), and the next launch resumes the parked rays first, side by side with
-// fresh ones in full warps.  A pixel's own sequence of segments is unchanged, only later: the image is
-// bit-identical; the host runs extra iterations until no pixel is live.
-constexpr int WF_CARRY_HEADER = 16;                         // ints before the stack in a parked-ray record
-constexpr int WF_CARRY_INTS = WF_CARRY_HEADER + RTB_STACK;  // slot cur leaf top sp t u v code - - - - - - - | stack
-static_assert(WF_CARRY_INTS == RTB_WF_CARRY_INTS, "rtb_launch.h sizes the parked-ray arrays");
-
-template <bool BRUTE, bool COUNT, bool CARRY>
+template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_traverse_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const unsigned int FULL = 0xffffffffu;
-    const unsigned int n_resume = CARRY ? min(*p.carry_n_in, (unsigned int)p.carry_cap) : 0u;  // parked by the previous launch
-    const unsigned int n = *p.tn + n_resume;  // the launch's work list: parked rays first, then the traversal queue
-    int budget = p.carry_budget;
+    const unsigned int n = *p.tn;
     const unsigned int lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // the counters the next wf_shade appends to
         *p.n_out = 0;
@@ -208,10 +183,8 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
             unsigned int mine = pos + __popc(want & ((1u << lane) - 1u));
             bool fresh = slot < 0 && mine < n;
             if (pos + __popc(want) >= n) exhausted = true;
-            const int *rec = nullptr;
-            if (CARRY && fresh && mine < n_resume) rec = p.carry_in + (size_t)mine * WF_CARRY_INTS;
             if (fresh) {
-                slot = rec ? rec[0] : p.tqueue[mine - n_resume];
+                slot = p.tqueue[mine];
                 float4 o = p.st.O[slot], d = p.st.D[slot], h = p.st.H[slot];
                 ray.o = v3(o.x, o.y, o.z);
                 ray.d = v3(d.x, d.y, d.z);
@@ -223,11 +196,6 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
                     // wf_shade left the best large-primitive hit in H: only the tree remains
                     T.best.t = h.x; T.best.u = h.y; T.best.v = h.z; T.best.code = __float_as_int(h.w);
                     trav_start_below_root(T, __float_as_int(o.w), __float_as_int(d.w));
-                    if (CARRY && rec) {  // a parked ray: back to where it stopped
-                        T.cur = rec[1]; T.leaf = rec[2]; T.top = rec[3]; T.sp = rec[4];
-                        T.best.t = __int_as_float(rec[5]); T.best.u = __int_as_float(rec[6]); T.best.v = __int_as_float(rec[7]); T.best.code = rec[8];
-                        for (int k = 0; k < T.sp; k++) T.stack[k] = rec[WF_CARRY_HEADER + k];
-                    }
                 }
             }
             busy = slot >= 0 && !trav_done(T);
@@ -251,34 +219,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
         // all 32 lanes enter together (lanes without a ray hold a finished state): while the queue has
         // rays, leave the tree when `refill` lanes are free; afterwards run to the end
         // (the quota counts finished lanes of the whole warp: the lanes that are free now, plus at least one)
-        if (!BRUTE) {
-            if (CARRY && exhausted && budget >= 0) {
-                // the tail: a bounded number of NODE iterations, then park what is left
-                trav_run<2, true>(s, ray, T, FULL, 0, p.walk_min, cnt, budget);
-                budget = 0;
-                bool left = slot >= 0 && !trav_done(T);
-                unsigned int left_mask = __ballot_sync(FULL, left);
-                if (left_mask) {
-                    unsigned int pos = 0;
-                    if (lane == 0) pos = atomicAdd(p.carry_n_out, (unsigned int)__popc(left_mask));
-                    pos = __shfl_sync(FULL, pos, 0) + __popc(left_mask & ((1u << lane) - 1u));
-                    bool park = left && pos < (unsigned int)p.carry_cap;
-                    if (park) {
-                        int *out = p.carry_out + (size_t)pos * WF_CARRY_INTS;
-                        out[0] = slot; out[1] = T.cur; out[2] = T.leaf; out[3] = T.top; out[4] = T.sp;
-                        out[5] = __float_as_int(T.best.t); out[6] = __float_as_int(T.best.u); out[7] = __float_as_int(T.best.v); out[8] = T.best.code;
-                        for (int k = 0; k < T.sp; k++) out[WF_CARRY_HEADER + k] = T.stack[k];
-                        p.st.H[slot] = make_float4(T.best.t, T.best.u, T.best.v, __int_as_float(WF_PENDING));
-                        slot = -1;
-                        T.cur = RTB_DONE; T.leaf = 0;
-                    }
-                    // no room left in the record array: those rays run to the end here, as without CARRY
-                    if (__any_sync(FULL, left && !park)) budget = -1;
-                }
-            } else {
-                trav_run<2>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
-            }
-        }
+        if (!BRUTE) trav_run<2>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
 #endif
     }
     if (COUNT && p.counters) {
@@ -367,14 +308,11 @@ cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int block
 
 cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {
     if (brute) {
-        if (count) wf_traverse_kernel<true, true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<true, false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-    } else if (p.carry_cap > 0) {
-        if (count) wf_traverse_kernel<false, true, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<false, false, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        if (count) wf_traverse_kernel<true, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
     } else {
-        if (count) wf_traverse_kernel<false, true, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
-        else wf_traverse_kernel<false, false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        if (count) wf_traverse_kernel<false, true><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
+        else wf_traverse_kernel<false, false><<<blocks, RTB_BLOCK_THREADS, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
@@ -382,5 +320,5 @@ cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int bl
 cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm) {
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false, false>, 256, 0);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false, false>, RTB_BLOCK_THREADS, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false>, RTB_BLOCK_THREADS, 0);
 }

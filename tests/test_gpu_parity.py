@@ -517,47 +517,3 @@ def test_big_mesh_flattened_by_host_threads(tracer):
     finally:
         tracer.set_option("strict_fp", 0)
         tracer.set_option("traversal", 0)
-
-
-@pytest.mark.parametrize("sid,p0,p1", [(0, 0, 0), (3, 0, 0), (6, 12, 10), (7, 0, 0)])
-def test_wavefront_parked_rays_are_bit_identical(tracer, sid, p0, p1):
-    """option wf_carry = N: a traversal warp that finds the queue empty parks the rays it has not finished after N
-    more NODE iterations; the next launch resumes them and wf_shade leaves their pixels alone meanwhile.  A
-    pixel's sequence of segments is only delayed: images, progressive frames and counters equal the plain
-    wavefront loop's, for tiny budgets (many parked rays), with a record array that overflows, and sharded."""
-    scene = _scene(sid, p0, p1)
-    try:
-        tracer.set_option("kernel", 1)
-        tracer.setup(scene, W, H, 3, 6)
-        out = []
-        parked = 0
-        for carry, cap in ((0, 65536), (1, 65536), (6, 65536), (64, 65536), (1, 1024)):
-            tracer.set_option("wf_carry", carry)
-            tracer.set_option("wf_carry_cap", cap)
-            tracer.set_option("counters", 1)
-            img = np.zeros((H, W, 3), np.float32)
-            f = tracer.render(img, 0, 4242)
-            c = tracer.counters()
-            tracer.set_option("counters", 0)
-            parked += int(tracer.info("wf_extra_iterations")) if carry == 1 else 0
-            f = tracer.render(img, f, 17)
-            out.append((img, c))
-        for img, c in out[1:]:
-            assert (img == out[0][0]).all()
-            for k in ("segments", "hit_segments", "samples"):
-                assert c[k] == out[0][1][k]
-        if sid in (0, 6):
-            assert parked > 0, "a budget of one NODE iteration should park rays and need extra iterations"
-        # sharded rows with parked rays
-        tracer.set_option("wf_carry", 2)
-        full = np.zeros((H, W, 3), np.float32)
-        tracer.render(full, 0, 5)
-        tracer.set_shard(1, 3, 8)
-        part = np.zeros((H, W, 3), np.float32)
-        tracer.render(part, 0, 5)
-        rows = [y for y in range(H) if (y // 8) % 3 == 1]
-        assert (part[rows] == full[rows]).all()
-    finally:
-        tracer.set_shard(0, 1, 8)
-        for k, v in (("kernel", 2), ("wf_carry", 0), ("wf_carry_cap", 65536), ("counters", 0)):
-            tracer.set_option(k, v)
