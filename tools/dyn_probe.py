@@ -1,4 +1,4 @@
-"""commit cost of dynamic scenes (diagnostic; run on the GPU box): python tests/dyn_probe.py"""
+"""commit cost of dynamic scenes (diagnostic; run on the GPU box): python tools/dyn_probe.py"""
 import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np

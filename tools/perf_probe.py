@@ -69,44 +69,3 @@ if __name__ == "__main__":
             run(*C3, opts={"kernel": 0, "builder": 1, "walk_min": wm})
         run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1, "builder": 0, "walk_min": 20})
         sys.exit(0)
-    if which == "lanes":
-        for r in (8, 16, 24):
-            run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": r})
-        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 16, "node_exit": 0})
-        run(*C3, opts={"kernel": 1, "builder": 1, "wf_refill": 16, "node_exit": 8})
-        run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": 1, "builder": 0})
-        sys.exit(0)
-    if which == "sweep6":
-        for r in (4, 8, 16):
-            for ne in (0, 4):
-                run(*C3, opts={"kernel": 1, "wf_refill": r, "node_exit": ne})
-        run(*C3, opts={"kernel": 0})
-        for b, ls in ((1, 1), (1, 0)):
-            run(*C3, opts={"kernel": 1, "builder": b, "large_split": ls})
-        for bps in (4, 6):
-            run(*C3, opts={"kernel": 1, "blocks_per_sm": bps})
-        for kern in (0, 1):
-            run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern})
-            run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern})
-            run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern})
-        sys.exit(0)
-    if which == "sweep5":
-        for kern in (0, 1):
-            for lm in (4, 8, 12, 16, 20, 24):
-                run(*C3, opts={"kernel": kern, "leaf_min": lm})
-        for r in (1, 2, 4, 8, 16):
-            run(*C3, opts={"kernel": 1, "wf_refill": r})
-        for r in (4, 8, 16, 24):
-            run(*C3, opts={"kernel": 0, "refill": r})
-        for kern in (0, 1):
-            for b, ls in ((1, 1), (1, 0), (0, 0)):
-                run(*C3, opts={"kernel": kern, "builder": b, "large_split": ls})
-        for kern in (0, 1):
-            run("C1", 0, 0, 0, 1000, 800, 32, 5, opts={"kernel": kern})
-            run("C2", 5, 0, 0, 1920, 1080, 16, 8, opts={"kernel": kern})
-            run("C4-small", 6, 40, 35, 1920, 1080, 4, 8, opts={"kernel": kern})
-        sys.exit(0)
-    run("C1", 0, 0, 0, 1000, 800, 100, 5)
-    run("C2", 5, 0, 0, 1920, 1080, 64, 8)
-    run("C3", 0, 0, 0, 1920, 1080, 64, 8)
-    run("C4-small", 6, 40, 35, 1920, 1080, 4, 8)
