@@ -49,6 +49,71 @@ __global__ void ref_primary_ids_kernel(int32_t *obj_id, float *t_out) {
     t_out[y * SCREEN_WIDTH + x] = best_t;
 }
 
+// primary-hit sub ids: for the winning object, which of its triangles the reference's own
+// Triangle::hit accepts -- quad 0/1 (t1 if it hits, else t2, src/objects.cu:229-233), cuboid face*2 + {0,1}
+// (closest face by strict <, :315), mesh = brute force over its triangles in index order with strict <
+__global__ void ref_primary_sub_ids_kernel(const int32_t *obj_id, int32_t *sub_id) {
+    int x = threadIdx.x + blockIdx.x * blockDim.x, y = threadIdx.y + blockIdx.y * blockDim.y;
+    if (x >= SCREEN_WIDTH || y >= SCREEN_HEIGHT) return;
+    int best = obj_id[y * SCREEN_WIDTH + x];
+    int sub = -1;
+    if (best >= 0) {
+        uint rng_state = 0;
+        Ray ray(x, y, &rng_state, false);
+        Object &o = const_objects.meshes[best];
+        sub = 0;
+        if (o.type == Object::QUAD) {
+            sub = o.quad.t1.hit(&ray).ray_hits ? 0 : 1;
+        } else if (o.type == Object::ONE_WAY_QUAD) {
+            sub = o.one_way_quad.t1.hit(&ray).ray_hits ? 0 : 1;
+        } else if (o.type == Object::CUBOID) {
+            float bt = INF;
+            for (int f = 0; f < 6; f++) {
+                RayHitData fh = o.cuboid.faces[f].hit(&ray);
+                if (fh.ray_hits && fh.ray_travelled_dist < bt) {
+                    bt = fh.ray_travelled_dist;
+                    sub = f * 2 + (o.cuboid.faces[f].t1.hit(&ray).ray_hits ? 0 : 1);
+                }
+            }
+        } else if (o.type == Object::MESH) {
+            float bt = INF;
+            sub = -1;
+            for (int k = 0; k < o.mesh.num_triangles; k++) {
+                RayHitData th = o.mesh.device_triangles[k].hit(&ray);
+                if (th.ray_hits && th.ray_travelled_dist < bt) { bt = th.ray_travelled_dist; sub = k; }
+            }
+        }
+    }
+    sub_id[y * SCREEN_WIDTH + x] = sub;
+}
+
+// The Mrays/s denominator counted by the reference's own code on the GPU: the loops of get_ray_colour /
+// trace_ray (src/raytracer.cu:67-105) with a segment and a hit counter, calling only reference functions.
+// Never used for radiance.
+__global__ void ref_count_segments_kernel(const int *current_time, unsigned long long *out) {
+    int x = threadIdx.x + blockIdx.x * blockDim.x, y = threadIdx.y + blockIdx.y * blockDim.y;
+    if (x >= SCREEN_WIDTH || y >= SCREEN_HEIGHT) return;
+    int array_index = (y * SCREEN_WIDTH + x) * 3;
+    uint rng_state = array_index * 3145739 + *current_time * 6291469;
+    Ray primary(x, y, &rng_state, const_render_data.antialias);
+    unsigned long long segments = 0, hits = 0;
+    for (int s = 0; s < const_render_data.rays_per_pixel; s++) {
+        Ray ray = primary;
+        Vec3 current_ray_colour(1, 1, 1);
+        for (int b = 0; b < const_render_data.reflection_limit; b++) {
+            ray.apply_antialias();
+            RayCollision collision = get_ray_collision(&ray);
+            segments++;
+            if (!collision.hit_data.ray_hits) break;
+            hits++;
+            Material material = collision.hit_mesh_material;
+            update_ray(&ray, &collision.hit_data, material);
+        }
+    }
+    atomicAdd(out, segments);
+    atomicAdd(out + 1, hits);
+}
+
 extern "C" {
 
 const char *refc_last_error() { return g_err.c_str(); }
@@ -138,6 +203,51 @@ int refc_primary_ids(int32_t *obj_id, float *t) {
         check_cuda_error(cudaMemcpy(t, d_t, n * 4, cudaMemcpyDeviceToHost), "ids");
         cudaFree(d_obj);
         cudaFree(d_t);
+        return 0;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// like refc_primary_ids, plus the sub id of the winning primitive (brute force over a mesh's triangles: small scenes only)
+int refc_primary_sub_ids(const int32_t *obj_id, int32_t *sub_id) {
+    try {
+        int32_t *d_obj, *d_sub;
+        size_t n = (size_t)SCREEN_WIDTH * SCREEN_HEIGHT;
+        check_cuda_error(cudaMalloc((void **)&d_obj, n * 4), "sub ids");
+        check_cuda_error(cudaMalloc((void **)&d_sub, n * 4), "sub ids");
+        check_cuda_error(cudaMemcpy(d_obj, obj_id, n * 4, cudaMemcpyHostToDevice), "sub ids");
+        dim3 thread_dim(8, 8);
+        dim3 block_dim = get_block_size(SCREEN_WIDTH, SCREEN_HEIGHT, thread_dim);
+        ref_primary_sub_ids_kernel<<<block_dim, thread_dim>>>(d_obj, d_sub);
+        check_cuda_error(cudaDeviceSynchronize(), "sub ids kernel");
+        check_cuda_error(cudaMemcpy(sub_id, d_sub, n * 4, cudaMemcpyDeviceToHost), "sub ids");
+        cudaFree(d_obj);
+        cudaFree(d_sub);
+        return 0;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// path segments ("rays") and hit segments of one frame at the current settings, counted by the reference's
+// own functions on the GPU (the bench's Mrays/s denominator for the reference arm; untimed)
+int refc_count_segments(int time_ms, unsigned long long *segments, unsigned long long *hits) {
+    try {
+        unsigned long long *d_out, h_out[2] = {0, 0};
+        check_cuda_error(cudaMalloc((void **)&d_out, sizeof h_out), "segment counters");
+        check_cuda_error(cudaMemcpy(d_out, h_out, sizeof h_out, cudaMemcpyHostToDevice), "segment counters");
+        check_cuda_error(cudaMemcpy(g_time, &time_ms, sizeof(int), cudaMemcpyHostToDevice), "time upload");
+        dim3 thread_dim(8, 8);
+        dim3 block_dim = get_block_size(SCREEN_WIDTH, SCREEN_HEIGHT, thread_dim);
+        ref_count_segments_kernel<<<block_dim, thread_dim>>>(g_time, d_out);
+        check_cuda_error(cudaDeviceSynchronize(), "segment counting kernel");
+        check_cuda_error(cudaMemcpy(h_out, d_out, sizeof h_out, cudaMemcpyDeviceToHost), "segment counters");
+        cudaFree(d_out);
+        *segments = h_out[0];
+        *hits = h_out[1];
         return 0;
     } catch (std::exception &e) {
         g_err = e.what();

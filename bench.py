@@ -66,14 +66,15 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, interval_ms=200):
         self.proc = None
         self.lines = []
         self.gpu = gpu_index
+        self.interval_ms = interval_ms
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", str(self.interval_ms),
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -124,28 +125,29 @@ def bytes_per_ray(c):
     return (32.0 * c["box_tests"] + 48.0 * c["tri_tests"] + 16.0 * c["sphere_tests"]) / seg
 
 
+SKY = (0.8, 1.0, 1.0)  # SKY_COLOUR, src/main.cu:13
+
+
 def cpu_baseline_leg(workload, threads):
     """The reference's own source on the host cores (oracle/_ref), else the C port: a bounded band of
-    the same workload at a few spp.  Returns the cpu_baseline object."""
+    the same workload at a few spp.  Returns the cpu_baseline object.  Loads the product only for the port."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import ctypes
     import numpy as np
     import oracle_binding as ob
-    import raytracer_b200 as rtb
     sid, p0, p1, W, H, spp, bounces = WORKLOADS[workload]
     if sid == 6:
         p0, p1 = 6, 5  # the host BVH of the full grid takes minutes to build; a 6x5 grid is the sample
     # 8 bands of H/128 rows spread evenly over the frame (1/16 of the pixels)
     nb, band = 8, max(1, H // 128)
     bands = [((2 * b + 1) * H // (2 * nb) - band // 2, (2 * b + 1) * H // (2 * nb) - band // 2 + band) for b in range(nb)]
-    scene = rtb.Scene(sid, p0, p1)
     sample_spp = 4  # about 10 s of single-threaded CPU work on the C3 sample
-    rd = scene.render_settings(sample_spp, bounces)
     rays, dt = 0, 0.0
     if ob.have_ref_host():
         ref = ob.RefHost()
         ref.build_scene(sid, p0, p1)
-        ref.set_render(rd)
+        sky = SKY if ref.L.refh_use_sky() else (0.0, 0.0, 0.0)
+        ref.L.refh_set_render(sample_spp, bounces, 1, *sky)
         ref.set_camera(W, H)
         out = np.zeros((H, W, 3), np.float32)
         for y0, y1 in bands:
@@ -157,6 +159,9 @@ def cpu_baseline_leg(workload, threads):
             rays += seg.value
         kind = "reference"
     else:
+        import raytracer_b200 as rtb
+        scene = rtb.Scene(sid, p0, p1)
+        rd = scene.render_settings(sample_spp, bounces)
         orc = ob.Oracle(scene)
         for y0, y1 in bands:
             cnt = rtb.Counters()
@@ -170,15 +175,23 @@ def cpu_baseline_leg(workload, threads):
                       + (" (6x5 instance grid)" if sid == 6 else "")}
 
 
+KERNEL_NAMES = {0: ["render_megakernel"], 1: ["wf_traverse", "wf_shade"], 3: ["pool_render"]}
+
+
 def ncu_traffic(workload, kernel_kind):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the two wavefront kernels, from the committed
-    `ncu --set full` summaries (profiles/r1e_ncu_*_C3.txt: launch 46 of a 4-spp C3 run); None for other workloads."""
-    if workload != "C3" or kernel_kind != 1:
-        return None
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the render kernels.  NOT measured by this run (a
+    number taken under a profiler is never a bench value, and ncu cannot run inside the timed process): read from the
+    committed `ncu --set full` summaries of the same kernels on the same workload, newest round first, and labelled
+    "source": "static ..."; None when no capture of this workload / kernel is committed."""
     out = {}
-    for kern in ("wf_traverse", "wf_shade"):
-        path = os.path.join(ROOT, "profiles", f"r1e_ncu_{kern}_C3.txt")
-        if not os.path.exists(path):
+    for kern in KERNEL_NAMES.get(kernel_kind, []):
+        path = None
+        for rnd in ("r2", "r1e"):
+            cand = os.path.join(ROOT, "profiles", f"{rnd}_ncu_{kern}_{workload}.txt")
+            if os.path.exists(cand):
+                path = cand
+                break
+        if path is None:
             return None
         total = 0.0
         for ln in open(path):
@@ -186,13 +199,36 @@ def ncu_traffic(workload, kernel_kind):
                 val, unit = ln.split(",", 1)[1].split()[:2]
                 total += float(val) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
         out[kern + "_kernel"] = total
+        out.setdefault("files", []).append(os.path.relpath(path, ROOT))
+    if not out:
+        return None
     out["unit"] = "bytes per launch"
-    out["source"] = "profiles/r1e_ncu_wf_traverse_C3.txt, profiles/r1e_ncu_wf_shade_C3.txt (ncu --set full, launch 46 of a 4-spp C3 frame: ~2 M live pixels)"
+    out["source"] = "static: committed ncu --set full summaries of the same kernels on this workload (see files), not measured in this run"
     return out
 
 
+def workload_config(workload):
+    """config of the JSON line: what one step computes.  Identical in the product arm and the reference arm."""
+    sid, p0, p1, W, H, spp, bounces = WORKLOADS[workload]
+    return {"workload": f"{workload}: {WORKLOAD_DESC[workload]}", "scene_id": sid, "width": W, "height": H, "spp_per_step": spp,
+            "bounces": bounces,
+            "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"}
+
+
+def reference_step_spp(workload, requested):
+    """spp per step of the reference arm: the workload's own (same config as the product arm) whenever a step of the
+    reference then stays under ~10 s; the 4K configs, where its fixed-depth BVH degenerates, are bounded
+    and reported as a rate."""
+    if requested:
+        return requested
+    spp = WORKLOADS[workload][5]
+    return {"C4": 1, "C5": min(spp, 32)}.get(workload, spp)
+
+
 def reference_arm(args):
-    """--impl reference.  Rank 0 only."""
+    """--impl reference: the reference's own CUDA build (baseline/_ref: unmodified sources, only the two resolution
+    constants patched) on the product arm's config.  Rank 0 only.  Nothing of the product is loaded: the rays of a step
+    are counted by the reference's own functions (refc_count_segments)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -203,20 +239,14 @@ def reference_arm(args):
     base = {"impl": "reference", "metric": "Mrays/s", "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic"}
+    config = workload_config(args.workload)
     threads = os.cpu_count() or 1
     if os.path.exists(ob.ref_cuda_path(W, H)):
-        import raytracer_b200 as rtb
-        # rays per frame from our counter build at the bounded spp (identical inputs, untimed)
-        ref_spp = args.ref_spp
-        scene = rtb.Scene(sid, p0, p1)
-        tr = rtb.Tracer(0).setup(scene, W, H, ref_spp, bounces)
-        tr.set_option("counters", 1)
-        tr.render_device(1, 1000)
-        tr.sync()
-        rays = tr.counters()["segments"]
-        tr.close()
+        ref_spp = reference_step_spp(args.workload, args.ref_spp)
+        config["spp_per_step"] = ref_spp
         ref = ob.RefCuda(W, H)
         ref.init(sid, p0, p1, ref_spp, bounces, True)
+        rays, _hits = ref.count_segments(1000)   # same inputs as the first timed step, untimed
         img = np.zeros((H, W, 3), np.float32)
         sampler = ClockSampler(0)
         for k in range(args.warmup):
@@ -224,31 +254,198 @@ def reference_arm(args):
         sampler.start()
         kernel_ms = [ref.render_kernel(img, 0, 1000 + k) for k in range(args.steps)]
         clocks = sampler.stop()
-        # end to end through the reference's own render() (src/dispatch.cu:156): wall clock
-        frame, wall = 0, []
+        ms_step = sum(kernel_ms) / len(kernel_ms)
+        # end to end through the reference's own render() (src/dispatch.cu:156), host image in and out: wall clock,
+        # same spp per step; as many of the K steps as fit in ~2.5 minutes
+        e2e_steps = max(1, min(args.steps, int(150.0 / max(ms_step / 1e3, 1e-3))))
         img2 = np.zeros((H, W, 3), np.float32)
         ref.render(img2, 0, 899)
-        for k in range(args.steps):
-            frame, ms = ref.render(img2, 0, 1000 + k)
+        wall = []
+        for k in range(e2e_steps):
+            img2[:] = 0
+            _, ms = ref.render(img2, 0, 1000 + k)
             wall.append(ms)
-        ms_step = sum(kernel_ms) / len(kernel_ms)
         value = rays / ms_step / 1e3
         e2e = rays / (sum(wall) / len(wall)) / 1e3
         nbytes = W * H * 3 * 4
-        line = dict(base, value=value, ms_per_step=ms_step, clocks=clocks, gpu_launches=args.steps,
+        line = dict(base, value=value, ms_per_step=ms_step, clocks=clocks, gpu_launches=args.steps, rays_per_step=rays,
                     spp_per_s_1080p=(ref_spp / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
                     e2e={"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes + 8, "d2h_bytes_per_step": nbytes,
+                         "ms_per_step": sum(wall) / len(wall), "steps": e2e_steps,
                          "note": "reference render(): per-frame cudaMalloc + H2D of previous_render, managed-memory read-back"},
-                    config={"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "reference_build": "the reference's own CUDA kernel get_pixel_colour, nvcc -arch=sm_100, default flags",
-                            "spp_per_step": ref_spp, "rays_per_step": rays, "note": "Mrays/s is a rate: spp per step is bounded so that a step stays ~1-3 s",
-                            "l2": "working set is L2-resident by design; see DESIGN.md"},
-                    cpu_baseline=cpu_baseline_leg(args.workload, threads))
+                    config=config,
+                    reference_build="the reference's own CUDA kernel get_pixel_colour, nvcc -arch=sm_100, default flags; stock launch shape and render()",
+                    cpu_baseline=None if args.no_cpu_baseline else cpu_baseline_leg(args.workload, threads))
     else:
         cb = cpu_baseline_leg(args.workload, threads)
         line = dict(base, value=cb["value"], ms_per_step=None, cpu_baseline=cb, gpu_launches=0,
                     e2e={"value": cb["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                    config={"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "reference_build": "reference CUDA library absent; host build of the reference source"})
+                    config=config, reference_build="reference CUDA library absent; host build of the reference source")
     print(json.dumps(line), flush=True)
+
+
+KERNEL_DESC = {0: "persistent megakernel", 1: "wavefront: wf_shade + persistent wf_traverse per path segment",
+               3: "pooled persistent kernel: one launch per frame, per-warp slot pools"}
+
+
+class Job:
+    """One workload on this rank's GPU: scene, tracer, sharding and the exchange step of a frame."""
+
+    def __init__(self, args, workload, sharding, rank, world, local_rank, dist):
+        import torch
+        import raytracer_b200 as rtb
+        self.torch, self.dist, self.rank, self.world, self.local_rank = torch, dist, rank, world, local_rank
+        self.workload = workload
+        sid, p0, p1, W, H, spp, bounces = WORKLOADS[workload]
+        self.W, self.H, self.spp, self.bounces = W, H, spp, bounces
+        if sharding == "auto":
+            sharding = "tiles" if W * H >= 3840 * 2160 else "slices"
+        if world == 1:
+            sharding = "none"
+        self.sharding = sharding
+        self.tiles, self.slices = sharding == "tiles", sharding == "slices"
+        self.band_rows = args.band_rows
+        self.scene = rtb.Scene(sid, p0, p1)
+        self.tr = tr = rtb.Tracer(local_rank)
+        if args.kernel is not None:
+            tr.set_option("kernel", args.kernel)
+        if args.builder is not None:
+            tr.set_option("builder", args.builder)
+        tr.setup(self.scene, W, H, spp, bounces)
+        if self.tiles:
+            tr.set_shard(rank, world, args.band_rows)
+        self.ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
+        rows_mine, rows_pad = tr.shard_rows()
+        self.dense = self.gathered = self.accum = None
+        with torch.cuda.stream(self.ext):
+            if self.tiles:
+                self.dense = torch.zeros(rows_pad * W * 3, device="cuda", dtype=torch.float32)
+                self.gathered = torch.empty(world * rows_pad * W * 3, device="cuda", dtype=torch.float32)
+            if self.slices:
+                class _Dev:  # the library's accumulation image as a torch tensor (no copy)
+                    __cuda_array_interface__ = {"shape": (H * W * 3,), "typestr": "<f4", "data": (tr.device_image_ptr(), False), "version": 2}
+                self.accum = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
+
+    def sharding_desc(self):
+        if self.world == 1:
+            return "none"
+        if self.tiles:
+            return f"tiles: row-cyclic bands of {self.band_rows} rows of one frame, NCCL all-gather per frame"
+        return (f"sample slices: {self.world} frames of {self.spp} spp per step (one per rank, own time seed), "
+                "NCCL all-reduce of the accumulation buffer per step")
+
+    def exchange(self):
+        """the one exchange step of a frame (on the library's stream); returns the kernels it launched"""
+        if self.tiles:
+            self.tr.shard_pack(self.dense.data_ptr())
+            self.dist.all_gather_into_tensor(self.gathered, self.dense)
+            self.tr.shard_unpack(self.gathered.data_ptr())
+            return 2
+        if self.slices:
+            self.dist.all_reduce(self.accum)      # sum of the ranks' running means ...
+            self.accum.mul_(1.0 / self.world)     # ... -> mean over world x spp samples
+            return 1
+        return 0
+
+    def frame_time(self, k):
+        return 1000 + k * (self.world if self.slices else 1) + (self.rank if self.slices else 0)
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, values, op="max"):
+        t = self.torch.tensor([float(v) for v in values], device="cuda", dtype=self.torch.float64)
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return t.tolist()
+
+    def count(self):
+        """op mix / ray count of one step: counter build, same inputs, untimed; summed over ranks"""
+        tr = self.tr
+        names = ("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples")
+        with self.torch.cuda.stream(self.ext):
+            tr.set_option("counters", 1)
+            tr.reset()
+            tr.render_device(1, self.frame_time(0))
+            tr.sync()
+            cnt = tr.counters()
+            tr.set_option("counters", 0)
+            vals = self.reduce([cnt[k] for k in names], "sum")
+        return dict(zip(names, [int(x) for x in vals]))
+
+    def device_step(self, k):
+        """one step, everything resident: render my share, then the exchange; returns launched kernels"""
+        self.tr.reset()
+        self.tr.render_device(1, self.frame_time(k))
+        return self.exchange()
+
+    def timed(self, steps, sample_ms=200, first_k=0):
+        """`steps` steps bracketed by barrier + synchronize, CUDA events on the library's stream, max over ranks.
+        Returns (ms per step, ms per step of the render kernels alone, launches, clocks of rank 0)."""
+        torch = self.torch
+        with torch.cuda.stream(self.ext):
+            per_frame = int(self.tr.info("launches_per_frame"))
+            self.barrier()
+            sampler = ClockSampler(self.local_rank, sample_ms)
+            if self.rank == 0:
+                sampler.start()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            launches = 0
+            ev0.record(self.ext)
+            for k in range(steps):
+                kev[k][0].record(self.ext)
+                self.tr.reset()
+                self.tr.render_device(1, self.frame_time(first_k + k))
+                kev[k][1].record(self.ext)
+                launches += per_frame + self.exchange()
+            ev1.record(self.ext)
+            self.barrier()
+            clocks = sampler.stop() if self.rank == 0 else None
+            ms_total = ev0.elapsed_time(ev1)
+            kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / steps
+            ms_total, kernel_ms = self.reduce([ms_total, kernel_ms], "max")
+        return ms_total / steps, kernel_ms, launches, clocks
+
+    def kernel_desc(self):
+        tr = self.tr
+        kind = int(tr.info("kernel"))
+        tuned = (f"auto: {KERNEL_DESC[kind].split(':')[0]} kept after timing the variants on a {min(self.spp, 8)}-spp frame "
+                 f"(pooled {tr.info('tune_pool_ms'):.2f} ms, wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
+                 if int(tr.info("kernel_tuned")) else "fixed by --kernel")
+        return kind, KERNEL_DESC[kind] + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), tuned
+
+    def close(self):
+        self.dense = self.gathered = self.accum = None
+        self.tr.close()
+
+
+def c4_tiles_record(args, rank, world, local_rank, dist):
+    """The strong-scaling configuration of BASELINE.json (config 4: 1 012 200 triangles at 3840x2160, screen tiles
+    with the image gathered over NCCL), measured in THIS run at THIS world size next to the headline: the 1-GPU line
+    is the denominator of the N = 2/4/8 lines.  16 spp per step (of the config's 1024: a rate)."""
+    import math
+    job = Job(args, "C4", "tiles", rank, world, local_rank, dist)
+    cnt = job.count()
+    with job.torch.cuda.stream(job.ext):
+        for k in range(3):
+            job.device_step(k)
+    ms_warm, _, _, _ = job.timed(2)
+    steps = max(5, min(400, int(math.ceil(4000.0 / max(ms_warm, 1e-3)))))   # >= 4 s timed: >= 20 clock samples at 100 ms
+    ms_step, kernel_ms, launches, clocks = job.timed(steps, sample_ms=100)
+    kind, kdesc, tuned = job.kernel_desc()
+    rec = None
+    if rank == 0:
+        rec = {"workload": f"C4: {WORKLOAD_DESC['C4']}", "metric": "Mrays/s", "value": cnt["segments"] / ms_step / 1e3, "unit": "Mrays/s",
+               "n_gpus": world, "scaling": "strong", "steps": steps, "warmup": 5, "ms_per_step": ms_step, "render_ms_per_step": kernel_ms,
+               "rays_per_step": cnt["segments"], "spp_per_step": job.spp, "sharding": job.sharding_desc(), "kernel": kdesc, "kernel_choice": tuned,
+               "prims": int(job.tr.info("num_prims")), "lbvh_build_ms": job.tr.info("build_ms"), "commit_ms": job.tr.info("commit_ms"),
+               "gather_bytes_per_step": (job.W * job.H * 3 * 4) if world > 1 else 0, "gpu_launches": launches, "clocks": clocks,
+               "op_mix_per_ray": {"box": cnt["box_tests"] / cnt["segments"], "tri": cnt["tri_tests"] / cnt["segments"]}}
+    job.close()
+    return rec
 
 
 def main():
@@ -260,9 +457,10 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--band-rows", type=int, default=8)
     ap.add_argument("--sharding", default="auto", choices=["auto", "tiles", "slices"])
-    ap.add_argument("--ref-spp", type=int, default=8, help="spp per step of the reference arm")
+    ap.add_argument("--ref-spp", type=int, default=0, help="spp per step of the reference arm (0 = the workload's own where a step stays under ~10 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront, 2 = timed choice between the two (library default)")
+    ap.add_argument("--no-c4-tiles", action="store_true", help="skip the C4 screen-tile record that rides along with the C3 headline")
+    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel, 2 = timed choice (library default)")
     ap.add_argument("--builder", type=int, default=None, help="0 = Karras LBVH, 1 = PLOC (library default)")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -272,7 +470,6 @@ def main():
 
     import numpy as np
     import torch
-    import raytracer_b200 as rtb
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -287,110 +484,20 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    sid, p0, p1, W, H, spp, bounces = WORKLOADS[args.workload]
-    sharding = args.sharding
-    if sharding == "auto":
-        sharding = "tiles" if W * H >= 3840 * 2160 else "slices"
-    if world == 1:
-        sharding = "none"
-    tiles, slices = sharding == "tiles", sharding == "slices"
-    scene = rtb.Scene(sid, p0, p1)
-    tr = rtb.Tracer(local_rank)
-    if args.kernel is not None:
-        tr.set_option("kernel", args.kernel)
-    if args.builder is not None:
-        tr.set_option("builder", args.builder)
-    tr.setup(scene, W, H, spp, bounces)
-    if tiles:
-        tr.set_shard(rank, world, args.band_rows)
-    ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
-    rows_mine, rows_pad = tr.shard_rows()
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    with torch.cuda.stream(ext):
-        dense = gathered = accum = None
-        if tiles:
-            dense = torch.zeros(rows_pad * W * 3, device="cuda", dtype=torch.float32)
-            gathered = torch.empty(world * rows_pad * W * 3, device="cuda", dtype=torch.float32)
-        if slices:
-            class _Dev:  # the library's accumulation image as a torch tensor (no copy)
-                __cuda_array_interface__ = {"shape": (H * W * 3,), "typestr": "<f4", "data": (tr.device_image_ptr(), False), "version": 2}
-            accum = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
-
-        def exchange():
-            """the one exchange step of a frame; returns the kernels it launched"""
-            if tiles:
-                tr.shard_pack(dense.data_ptr())
-                dist.all_gather_into_tensor(gathered, dense)
-                tr.shard_unpack(gathered.data_ptr())
-                return 2
-            if slices:
-                dist.all_reduce(accum)      # sum of the ranks' running means ...
-                accum.mul_(1.0 / world)     # ... -> mean over world x spp samples
-                return 1
-            return 0
-
-        def frame_time(k):
-            return 1000 + k * (world if slices else 1) + (rank if slices else 0)
-
-        def device_step(k):
-            """one step, everything resident: render my share, then the exchange"""
-            tr.reset()
-            tr.render_device(1, frame_time(k))
-            exchange()
-
-        # op mix / ray count of one step: counter build, same inputs, untimed
-        tr.set_option("counters", 1)
-        tr.reset()
-        tr.render_device(1, frame_time(0))
-        tr.sync()
-        cnt = tr.counters()
-        tr.set_option("counters", 0)
-        t = torch.tensor([float(cnt[k]) for k in ("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples")],
-                         device="cuda", dtype=torch.float64)
-        if dist is not None:
-            dist.all_reduce(t)
-        cnt = dict(zip(("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples"), [int(x) for x in t.tolist()]))
-        rays_per_step = cnt["segments"]
-
+    job = Job(args, args.workload, args.sharding, rank, world, local_rank, dist)
+    tr, W, H, spp = job.tr, job.W, job.H, job.spp
+    cnt = job.count()
+    rays_per_step = cnt["segments"]
+    with torch.cuda.stream(job.ext):
         for k in range(args.warmup):
-            device_step(k)
-        barrier()
-        # with option "kernel" = 2 (the default) the first warm-up frame timed both variants on this rank's
-        # share of the workload and kept the faster; from here on the choice is fixed
-        kernel_kind = int(tr.info("kernel"))
-        per_frame = int(tr.info("launches_per_frame"))
-        tuned = (f"auto: {'wavefront' if kernel_kind == 1 else 'megakernel'} kept after timing both on a {min(spp, 8)}-spp frame "
-                 f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
-                 if int(tr.info("kernel_tuned")) else "fixed by --kernel")
-        sampler = ClockSampler(local_rank)
-        if rank == 0:
-            sampler.start()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        launches = 0
-        ev0.record(ext)
-        for k in range(args.steps):
-            kev[k][0].record(ext)
-            tr.reset()
-            tr.render_device(1, frame_time(k))
-            kev[k][1].record(ext)
-            launches += per_frame + exchange()
-        ev1.record(ext)
-        barrier()
-        clocks = sampler.stop() if rank == 0 else None
-        ms_total = ev0.elapsed_time(ev1)
-        kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
-        tt = torch.tensor([ms_total, kernel_ms], device="cuda", dtype=torch.float64)
-        if dist is not None:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_total, kernel_ms = tt.tolist()
+            job.device_step(k)
+    # with option "kernel" = 2 (the default) the first warm-up frame timed the variants on this rank's share of the
+    # workload and kept the fastest; from here on the choice is fixed
+    ms_step, kernel_ms, launches, clocks = job.timed(args.steps)
+    kernel_kind, kernel_desc, tuned = job.kernel_desc()
 
-        # ---- end to end through the reference-facing entry point, host buffers ----
+    # ---- end to end through the reference-facing entry point, host buffers ----
+    with torch.cuda.stream(job.ext):
         host = torch.zeros(H * W * 3, dtype=torch.float32).pin_memory()
         himg = host.numpy()
         nbytes = H * W * 3 * 4
@@ -402,27 +509,30 @@ def main():
             else:
                 himg[:] = 0
                 tr.set_accumulation(himg, 0)  # H2D
-                tr.render_device(1, frame_time(k))
-                exchange()
+                tr.render_device(1, job.frame_time(k))
+                job.exchange()
                 out, _ = tr.download()  # D2H + sync
                 himg[:] = out.reshape(-1)
 
         e2e_step(0)
-        barrier()
+        job.barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
             e2e_step(k)
-        barrier()
-        e2e_ms = (time.perf_counter() - t0) * 1e3
-        te = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
-        if dist is not None:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e_ms = te.item()
+        job.barrier()
+        e2e_ms = job.reduce([(time.perf_counter() - t0) * 1e3], "max")[0]
         checksum = float(himg.astype(np.float64).sum())
         fp32_peak = tr.fp32_peak_tflops(40.0) if rank == 0 else None
+    info = {k: tr.info(k) for k in ("builder", "num_prims", "build_ms")}
+    sharding_desc = job.sharding_desc()
+    slices = job.slices
+    job.close()
+
+    c4 = None
+    if args.workload == "C3" and not args.no_c4_tiles:
+        c4 = c4_tiles_record(args, rank, world, local_rank, dist)
 
     if rank == 0:
-        ms_step = ms_total / args.steps
         value = rays_per_step / ms_step / 1e3                       # Mrays/s, whole job
         e2e_value = rays_per_step / (e2e_ms / args.steps) / 1e3
         fpr = flops_per_ray(cnt)
@@ -437,17 +547,14 @@ def main():
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if slices else "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "spp_per_s_1080p": (spp * (world if slices else 1) / (ms_step / 1e3)) if (W, H) == (1920, 1080) else None,
-            "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "scene_id": sid, "width": W, "height": H, "spp_per_step": spp,
-                       "bounces": bounces, "rays_per_step": rays_per_step, "segments_per_sample": cnt["segments"] / max(1, cnt["samples"]),
-                       "sharding": "none" if world == 1 else (f"tiles: row-cyclic bands of {args.band_rows} rows of one frame, NCCL all-gather per frame" if tiles else
-                                                                f"sample slices: {world} frames of {spp} spp per step (one per rank, own time seed), NCCL all-reduce of the accumulation buffer per step"),
-                       "kernel": ("wavefront: wf_shade + persistent wf_traverse per path segment" if kernel_kind == 1 else "persistent megakernel")
-                                 + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), "kernel_choice": tuned, "prims": int(tr.info("num_prims")), "lbvh_build_ms": tr.info("build_ms"),
-                       "l2": "scene is L2/L1-resident by design (not an HBM-bound path); the accumulation image is reset each step"},
+            "config": workload_config(args.workload),
+            "rays_per_step": rays_per_step, "segments_per_sample": cnt["segments"] / max(1, cnt["samples"]),
+            "sharding": sharding_desc, "kernel": kernel_desc, "kernel_choice": tuned, "prims": int(info["num_prims"]),
+            "lbvh_build_ms": info["build_ms"],
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
                     "ms_per_step": e2e_ms / args.steps, "checksum": checksum},
-            "roofline": {"bound": "fp32", "kernel": "wf_traverse_kernel + wf_shade_kernel (all launches of a step)" if kernel_kind == 1 else "render_megakernel",
+            "roofline": {"bound": "fp32", "kernel": " + ".join(n + "_kernel" for n in KERNEL_NAMES[kernel_kind]) + " (all launches of a step)",
                          "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak if fp32_peak else None,
                          "peak_kind": "measured FFMA microbenchmark on this GPU (rtb_measure_fp32_peak)", "peak_nominal": nominal_peak,
                          "frac_of_nominal": achieved_tf / nominal_peak, "traffic": ncu_traffic(args.workload, kernel_kind),
@@ -460,10 +567,11 @@ def main():
                                                        "measured dram bytes are in profiles/ (ncu)",
                                                "peak_kind": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"}},
         }
+        if c4 is not None:
+            line["c4_tiles"] = c4
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg(args.workload, 1)
         print(json.dumps(line), flush=True)
-    tr.close()
     if dist is not None:
         dist.destroy_process_group()
 

@@ -11,7 +11,6 @@ The directory name contains a hyphen (the repository layout asks for it); import
 """
 import ctypes
 import os
-import re
 
 import numpy as np
 
@@ -19,8 +18,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 
 
-class RtbError(RuntimeError):
-    """Mirrors the std::runtime_error the reference's check_cuda_error throws (src/utils.cu:5-10)."""
+from .abi import (ASSETS_DIR, MAT_EMISSIVE, MAT_REFRACTIVE, MAT_STANDARD, OBJ_CUBOID, OBJ_MESH, OBJ_ONE_WAY_QUAD, OBJ_QUAD,  # noqa: F401
+                  OBJ_SPHERE, OBJ_TRIANGLE, REF_MODELS_DIR, TEX_CHECKERBOARD, TEX_COLOUR, TEX_GRADIENT, TEX_IMAGE, CamData, Counters,
+                  Image, Material, Object, RenderData, RtbError, SceneDesc, Texture, Vec3, declared_symbols, models_dir)
 
 
 def _load(name):
@@ -34,61 +34,6 @@ def _load(name):
 
 lib = _load("librtb.so")
 scenes_lib = _load("librtb_scenes.so")
-
-
-class Vec3(ctypes.Structure):
-    _fields_ = [("x", ctypes.c_float), ("y", ctypes.c_float), ("z", ctypes.c_float)]
-
-
-class CamData(ctypes.Structure):  # RtbCamData == DeviceCamData (src/camera.cu:12-18)
-    _fields_ = [("cam_pos", Vec3), ("tl_pixel_pos", Vec3), ("delta_u", Vec3), ("delta_v", Vec3)]
-
-
-class RenderData(ctypes.Structure):  # RtbRenderData == RenderData (src/raytracer.cu:4-12)
-    _fields_ = [("rays_per_pixel", ctypes.c_int), ("reflection_limit", ctypes.c_int), ("antialias", ctypes.c_int),
-                ("sky_colour", Vec3)]
-
-
-class Texture(ctypes.Structure):
-    _fields_ = [("type", ctypes.c_int), ("colour", Vec3), ("light", Vec3), ("dark", Vec3), ("num_squares", ctypes.c_int),
-                ("img_width", ctypes.c_int), ("img_height", ctypes.c_int), ("image", ctypes.c_int)]
-
-
-class Material(ctypes.Structure):
-    _fields_ = [("type", ctypes.c_int), ("texture", Texture), ("smoothness", ctypes.c_float), ("need_uv", ctypes.c_int),
-                ("emitted_light", Vec3), ("refractive_index", ctypes.c_float)]
-
-
-class Object(ctypes.Structure):
-    _fields_ = [("type", ctypes.c_int), ("material", ctypes.c_int), ("p", Vec3 * 4), ("f", ctypes.c_float * 3),
-                ("uv", ctypes.c_float * 6), ("invert_normal", ctypes.c_int), ("tri_first", ctypes.c_int),
-                ("tri_count", ctypes.c_int)]
-
-
-class Image(ctypes.Structure):
-    _fields_ = [("width", ctypes.c_int), ("height", ctypes.c_int), ("rgb", ctypes.POINTER(ctypes.c_float))]
-
-
-class SceneDesc(ctypes.Structure):
-    _fields_ = [("num_objects", ctypes.c_int), ("objects", ctypes.POINTER(Object)),
-                ("num_materials", ctypes.c_int), ("materials", ctypes.POINTER(Material)),
-                ("num_mesh_tris", ctypes.c_int), ("mesh_tri_points", ctypes.POINTER(ctypes.c_float)),
-                ("mesh_tri_uv", ctypes.POINTER(ctypes.c_float)),
-                ("num_images", ctypes.c_int), ("images", ctypes.POINTER(Image))]
-
-
-class Counters(ctypes.Structure):
-    _fields_ = [(n, ctypes.c_ulonglong) for n in ("segments", "hit_segments", "box_tests", "tri_tests", "sphere_tests", "samples")]
-
-    def as_dict(self):
-        return {n: int(getattr(self, n)) for n, _ in self._fields_}
-
-
-def declared_symbols(header=os.path.join(REPO_ROOT, "include", "rtb.h")):
-    """Every function name include/rtb.h declares (used by the symbol-export test)."""
-    text = open(header).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(rtb_[a-z_0-9]+)\s*\(", text)))
 
 
 _vp, _i, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
@@ -158,26 +103,6 @@ scenes_lib.rtbs_camera.argtypes = [_i, _i, ctypes.POINTER(ctypes.c_float * 3), c
                                    ctypes.c_float, ctypes.POINTER(CamData)]
 scenes_lib.rtbs_camera.restype = None
 scenes_lib.rtbs_render_settings.argtypes = [_i, _i, _i, _i, ctypes.POINTER(RenderData)]
-
-
-# enums of include/rtb.h
-TEX_COLOUR, TEX_GRADIENT, TEX_CHECKERBOARD, TEX_IMAGE = 0, 1, 2, 3
-MAT_STANDARD, MAT_EMISSIVE, MAT_REFRACTIVE = 0, 1, 2
-OBJ_SPHERE, OBJ_TRIANGLE, OBJ_QUAD, OBJ_ONE_WAY_QUAD, OBJ_CUBOID, OBJ_MESH = 0, 1, 2, 3, 4, 5
-
-# this repo's own fixtures (OBJ + MTL, images, parsed-texture files); host/obj_mtl.hpp reads the variable
-ASSETS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets")
-os.environ.setdefault("RTB_ASSETS_DIR", ASSETS_DIR)
-
-
-def models_dir():
-    """Directory holding cube.obj / low_poly_monkey.obj (reference DATA, never committed here)."""
-    cands = [os.environ.get("RTB_MODELS_DIR"), os.path.join(REPO_ROOT, "oracle", "_ref", "models"),
-             "/root/reference/models"]
-    for c in cands:
-        if c and os.path.exists(os.path.join(c, "low_poly_monkey.obj")):
-            return c
-    raise RtbError("OBJ fixtures not found (set RTB_MODELS_DIR or run oracle/Makefile where /root/reference exists)")
 
 
 class Scene:

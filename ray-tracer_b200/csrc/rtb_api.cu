@@ -81,17 +81,26 @@ struct rtb_ctx {
     size_t wf_events_used = 0;
     double wf_shade_ms = 0, wf_traverse_ms = 0, wf_total_ms = 0;
 
+    // pooled persistent kernel: per-warp slot records (6 KB per warp of the grid)
+    float4 *d_pool = nullptr;
+    size_t pool_warps = 0;
+    int pool_per_sm = 0;
+
     // options
-    // 0 = persistent megakernel, 1 = wavefront, 2 = auto: both are timed on the first frame after the
-    // scene / resolution / settings / shard change and the faster is kept (they are bit-identical)
+    // 0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel, 2 = auto: the variants are timed on
+    // the first frame after the scene / resolution / settings / shard change and the fastest is kept (bit-identical)
     int opt_kernel = 2;
     int auto_choice = -1;                  // -1 = not tuned yet
-    double tune_ms[2] = {0, 0};            // [0] megakernel, [1] wavefront: device ms of the tuning frame
+    double tune_ms[4] = {0, 0, 0, 0};      // device ms of the tuning frame, by kernel id ([0] megakernel, [1] wavefront, [3] pooled)
+    int tuned_prims = -1;                  // primitive count the choice was tuned on
+    int opt_tune_set = 8 | 2 | 1;          // kernels the timed choice tries: bit k = kernel id k
+    float *d_tune_scratch = nullptr;       // scratch image of the tuning frames (kept: dynamic scenes re-tune)
+    size_t tune_scratch_floats = 0;
     int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24;
     // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (12, 16),
     // whichever the tuning frame measures faster (closed rooms prefer the second, the 1 M-triangle grid the first)
     int opt_walk_min = 0, opt_wf_refill = 0;
-    int tuned_wf_walk_min = 16, tuned_wf_refill = 8;
+    int tuned_walk_min = 16, tuned_refill = 8;
     int opt_builder = 1, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
     int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
     int shard_rank = 0, shard_world = 1, band_rows = 8;
@@ -435,6 +444,12 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num);
 
 int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num);
 
+int launch_frame_pool(rtb_ctx *c, int time_ms, int frame_num);
+
+int launch_kernel_variant(rtb_ctx *c, int kern, int time_ms, int frame_num) {
+    return kern == 1 ? launch_frame_wavefront(c, time_ms, frame_num) : kern == 3 ? launch_frame_pool(c, time_ms, frame_num) : launch_frame_megakernel(c, time_ms, frame_num);
+}
+
 // option "kernel" = 2: a short frame (RTB_TUNE_SPP samples per pixel of the real scene, camera, shard
 // and bounce limit) through each variant into a scratch image; the winner renders until something
 // that shapes the workload changes.  Which variant wins depends on the workload (long
@@ -446,55 +461,116 @@ int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num);
 bool wavefront_fits(const rtb_ctx *c) { return c->rd.reflection_limit <= 255 && (long long)c->rd.rays_per_pixel < (1 << 24); }
 
 int autotune_kernel(rtb_ctx *c) {
+    c->tuned_prims = c->d.num_prims;
     if (!wavefront_fits(c)) { c->auto_choice = 0; return 0; }
-    c->auto_choice = 1;
+    c->auto_choice = 3;
     if (c->opt_counters || c->image_floats == 0) return 0;  // counted builds are not timed
-    float *scratch = nullptr;
-    if (cudaMalloc((void **)&scratch, c->image_floats * sizeof(float)) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;  // no room for a scratch image: keep the wavefront kernels
+    if (c->tune_scratch_floats != c->image_floats) {
+        if (c->d_tune_scratch) cudaFree(c->d_tune_scratch);
+        c->d_tune_scratch = nullptr; c->tune_scratch_floats = 0;
+        if (cudaMalloc((void **)&c->d_tune_scratch, c->image_floats * sizeof(float)) != cudaSuccess) {
+            cudaGetLastError();
+            return 0;  // no room for a scratch image: keep the pooled kernel
+        }
+        c->tune_scratch_floats = c->image_floats;
     }
+    float *scratch = c->d_tune_scratch;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     float *image = c->d_image;
     const RtbRenderData rd = c->rd;
     c->d_image = scratch;
     int rc = 0;
-    // candidates: wavefront with two traversal policies, then the megakernel
-    struct Cand { int kern, walk_min, wf_refill; float ms; } cand[3] = {{1, 16, 8, 0.f}, {1, 12, 16, 0.f}, {0, 0, 0, 0.f}};
-    const int n_cand = 3;
-    for (int i = 0; i < n_cand && rc == 0; i++) {
-        if (cand[i].kern == 1) { c->tuned_wf_walk_min = cand[i].walk_min; c->tuned_wf_refill = cand[i].wf_refill; }
-        if (i == 1 && (c->opt_walk_min > 0 && c->opt_wf_refill > 0)) { cand[i].ms = 1e30f; continue; }  // both knobs pinned by the caller
-        for (int pass = (i == 1 ? 1 : 0); pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
+    // candidates: each kernel with its traversal policies (walk_min, refill); the megakernel has one
+    struct Cand { int kern, walk_min, refill; float ms; };
+    std::vector<Cand> cand;
+    if (c->opt_tune_set & 8) { cand.push_back({3, 16, 8, 0.f}); cand.push_back({3, 12, 16, 0.f}); }
+    if (c->opt_tune_set & 2) { cand.push_back({1, 16, 8, 0.f}); cand.push_back({1, 12, 16, 0.f}); }
+    if (c->opt_tune_set & 1) cand.push_back({0, 0, 0, 0.f});
+    const bool pinned = c->opt_walk_min > 0 && c->opt_wf_refill > 0;  // both knobs pinned by the caller: one policy per kernel
+    int warmed = 0;  // kernels whose first (1-spp) frame has run
+    for (size_t i = 0; i < cand.size() && rc == 0; i++) {
+        const bool second_policy = i > 0 && cand[i - 1].kern == cand[i].kern;
+        if (second_policy && pinned) { cand[i].ms = 1e30f; continue; }
+        c->tuned_walk_min = cand[i].walk_min; c->tuned_refill = cand[i].refill;
+        for (int pass = (warmed >> cand[i].kern) & 1; pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
             c->rd.rays_per_pixel = pass == 0 ? 1 : std::min(rd.rays_per_pixel, RTB_TUNE_SPP);
             cudaMemsetAsync(scratch, 0, c->image_floats * sizeof(float), c->stream);
             cudaEventRecord(e0, c->stream);
-            rc = cand[i].kern == 1 ? launch_frame_wavefront(c, 12345, 0) : launch_frame_megakernel(c, 12345, 0);
+            rc = launch_kernel_variant(c, cand[i].kern, 12345, 0);
             cudaEventRecord(e1, c->stream);
             if (rc == 0 && cudaStreamSynchronize(c->stream) != cudaSuccess) rc = fail(c, "tuning the kernel choice", cudaGetErrorString(cudaGetLastError()));
             float ms = 0;
             if (rc == 0) cudaEventElapsedTime(&ms, e0, e1);
             cand[i].ms = ms;
         }
+        warmed |= 1 << cand[i].kern;
     }
-    int wf = cand[1].ms < cand[0].ms ? 1 : 0;
-    c->tuned_wf_walk_min = cand[wf].walk_min; c->tuned_wf_refill = cand[wf].wf_refill;
-    c->tune_ms[1] = cand[wf].ms; c->tune_ms[0] = cand[2].ms;
     c->rd = rd;
     c->d_image = image;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    cudaFree(scratch);
-    if (rc != 0) { c->auto_choice = -1; return rc; }
-    c->auto_choice = c->tune_ms[0] < 0.97 * c->tune_ms[1] ? 0 : 1;
+    if (rc != 0 || cand.empty()) { c->auto_choice = rc != 0 ? -1 : 3; return rc; }
+    for (int k = 0; k < 4; k++) c->tune_ms[k] = 0;
+    size_t best = 0;
+    for (size_t i = 0; i < cand.size(); i++) {
+        if (cand[i].ms < cand[best].ms) best = i;
+        double &slot = c->tune_ms[cand[i].kern];
+        if (slot == 0 || cand[i].ms < slot) slot = cand[i].ms;
+    }
+    c->auto_choice = cand[best].kern;
+    c->tuned_walk_min = cand[best].walk_min; c->tuned_refill = cand[best].refill;
     return 0;
 }
 
-int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? (wavefront_fits(c) ? 1 : 0) : c->auto_choice) : c->opt_kernel; }
+int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? (wavefront_fits(c) ? 3 : 0) : c->auto_choice) : c->opt_kernel; }
 
 int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     if (c->opt_kernel == 2 && c->auto_choice < 0 && autotune_kernel(c) != 0) return 1;
-    return effective_kernel(c) == 1 ? launch_frame_wavefront(c, time_ms, frame_num) : launch_frame_megakernel(c, time_ms, frame_num);
+    return launch_kernel_variant(c, effective_kernel(c), time_ms, frame_num);
+}
+
+// One frame through the pooled persistent kernel (rtb_pool.cuh): one launch.
+int launch_frame_pool(rtb_ctx *c, int time_ms, int frame_num) {
+    if (!wavefront_fits(c) || c->width > 65535 || c->height > 65535)
+        return fail(c, "render", "the pooled kernel packs the bounce index in 8 bits, the sample index in 24 and a pixel coordinate in 16 "
+                                 "(reflection_limit <= 255, rays_per_pixel < 2^24, width and height < 65536): use option kernel = 0 or 2");
+    const bool strict_fp = c->opt_strict != 0;
+    if (c->pool_per_sm == 0) {
+        cudaError_t e = strict_fp ? strict::pool_occupancy(&c->pool_per_sm) : fast::pool_occupancy(&c->pool_per_sm);
+        if (e != cudaSuccess || c->pool_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
+    }
+    const int threads = strict_fp ? strict::pool_block_threads() : fast::pool_block_threads();
+    int per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->pool_per_sm) : c->pool_per_sm;
+    const int blocks = c->num_sms * per_sm;
+    const size_t warps = (size_t)blocks * (threads / 32);
+    if (c->pool_warps < warps) {
+        if (c->d_pool) cudaFree(c->d_pool);
+        c->d_pool = nullptr; c->pool_warps = 0;
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_pool, warps * 6 * 64 * sizeof(float4)), "allocating the slot pool");
+        c->pool_warps = warps;
+    }
+    PoolParams p;
+    p.scene = c->d;
+    std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
+    p.rd.rays_per_pixel = c->rd.rays_per_pixel;
+    p.rd.reflection_limit = c->rd.reflection_limit;
+    p.rd.antialias = c->rd.antialias;
+    p.rd.sky[0] = c->rd.sky_colour.x; p.rd.sky[1] = c->rd.sky_colour.y; p.rd.sky[2] = c->rd.sky_colour.z;
+    p.width = c->width; p.height = c->height;
+    p.time_ms = time_ms; p.frame_num = frame_num;
+    p.prev = c->d_image; p.out = c->d_image;
+    p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
+    p.local_rows = shard_local_rows(c, c->shard_rank);
+    p.refill = c->opt_wf_refill < 1 ? c->tuned_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
+    p.walk_min = c->opt_walk_min < 1 ? c->tuned_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
+    p.pool = c->d_pool;
+    p.work_counter = c->d_work;
+    p.counters = c->opt_counters ? c->d_counters : nullptr;
+    RTB_CUDA(c, cudaMemsetAsync(c->d_work, 0, sizeof(unsigned int), c->stream), "resetting work counter");
+    cudaError_t e = strict_fp ? strict::launch_pool(p, c->opt_traversal == 1, c->opt_counters != 0, blocks, c->stream)
+                              : fast::launch_pool(p, c->opt_traversal == 1, c->opt_counters != 0, blocks, c->stream);
+    if (e != cudaSuccess) return fail(c, "launching render kernel", cudaGetErrorString(e));
+    return 0;
 }
 
 int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num) {
@@ -571,8 +647,8 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     float4 *st = c->d_wf_state;
     base.st.A = st; base.st.B = st + slots; base.st.C = st + 2 * slots; base.st.O = st + 3 * slots; base.st.D = st + 4 * slots; base.st.H = st + 5 * slots;
     base.alive = c->d_wf_alive;
-    base.refill = c->opt_wf_refill < 1 ? c->tuned_wf_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
-    base.walk_min = c->opt_walk_min < 1 ? c->tuned_wf_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
+    base.refill = c->opt_wf_refill < 1 ? c->tuned_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
+    base.walk_min = c->opt_walk_min < 1 ? c->tuned_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
     base.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
     int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
@@ -779,6 +855,8 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->d_wf_counts) cudaFree(c->d_wf_counts);
     if (c->d_wf_alive) cudaFree(c->d_wf_alive);
     if (c->d_wf_block_count) cudaFree(c->d_wf_block_count);
+    if (c->d_pool) cudaFree(c->d_pool);
+    if (c->d_tune_scratch) cudaFree(c->d_tune_scratch);
     for (cudaEvent_t ev : c->wf_events) cudaEventDestroy(ev);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
@@ -926,7 +1004,6 @@ int rtb_scene_commit(rtb_ctx *c) {
 
 static int scene_commit_timed(rtb_ctx *c) {
     Bind b(c);
-    c->auto_choice = -1;
     cudaStreamSynchronize(c->stream);
     free_scene(c);
     Flat f;
@@ -1018,6 +1095,9 @@ static int scene_commit_timed(rtb_ctx *c) {
         RTB_CUDA(c, cudaMemcpy(d.root_node, nodes + 4 * (size_t)root, 4 * sizeof(float4), cudaMemcpyDeviceToHost), "reading the root node");
     c->d = d;
     c->committed = true;
+    // the timed kernel choice survives a commit that leaves the scene about the same size (dynamic scenes
+    // commit every frame); more than 2x more or fewer primitives tune again
+    if (c->tuned_prims < 0 || d.num_prims > 2 * (long long)c->tuned_prims || 2 * (long long)d.num_prims < c->tuned_prims) c->auto_choice = -1;
     return 0;
 }
 
@@ -1261,7 +1341,8 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     c->auto_choice = -1;  // every option shapes the kernels: tune again at the next frame
     if (k == "counters") c->opt_counters = value;
     else if (k == "traversal") c->opt_traversal = value;
-    else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; }
+    else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; c->pool_per_sm = 0; }
+    else if (k == "tune_set") c->opt_tune_set = value & 11;   // kernels the timed choice tries: 1 megakernel, 2 wavefront, 8 pooled
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
     else if (k == "builder") c->opt_builder = value;
     else if (k == "ploc_radius") c->opt_ploc_radius = value;
@@ -1275,7 +1356,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "wf_streams") c->opt_wf_streams = value < 1 ? 1 : value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
     else if (k == "kernel") {
-        if (value < 0 || value > 2) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice)");
+        if (value < 0 || value > 3) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice), 3 = pooled persistent kernel");
         c->opt_kernel = value;
     }
     else if (k == "block_threads") {
@@ -1327,8 +1408,9 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "kernel_tuned") *value = c->opt_kernel == 2 && c->auto_choice >= 0 ? 1 : 0;
     else if (k == "tune_megakernel_ms") *value = c->tune_ms[0];
     else if (k == "tune_wavefront_ms") *value = c->tune_ms[1];
-    else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) == 1 ? c->tuned_wf_walk_min : 8);
-    else if (k == "wf_refill") *value = c->opt_wf_refill > 0 ? c->opt_wf_refill : c->tuned_wf_refill;
+    else if (k == "tune_pool_ms") *value = c->tune_ms[3];
+    else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) != 0 ? c->tuned_walk_min : 8);
+    else if (k == "wf_refill") *value = c->opt_wf_refill > 0 ? c->opt_wf_refill : c->tuned_refill;
     else if (k == "wf_shade_ms") *value = c->wf_shade_ms;
     else if (k == "wf_traverse_ms") *value = c->wf_traverse_ms;
     else if (k == "wf_total_ms") *value = c->wf_total_ms;
@@ -1337,7 +1419,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
         double it = (double)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
         double rebuilds = c->opt_wf_rebuild > 0 && it > 0 ? std::floor((it - 1) / c->opt_wf_rebuild) : 0;
         int groups = std::max(1, std::min(c->opt_wf_groups, shard_local_rows(c, c->shard_rank)));
-        *value = effective_kernel(c) == 1 ? groups * (1.0 + 2.0 * it + 3.0 * rebuilds) : 1.0;
+        *value = effective_kernel(c) == 1 ? groups * (1.0 + 2.0 * it + 3.0 * rebuilds) : 1.0;  // megakernel and pooled kernel: one launch
     }
     else if (k.rfind("lane_stat", 0) == 0 && k.size() == 10 && k[9] >= '0' && k[9] <= '7') *value = (double)c->last_lane_stats[k[9] - '0'];
     else if (k == "scene_bytes") *value = (double)c->scene_bytes;

@@ -59,6 +59,22 @@ struct WfParams {
     unsigned long long *counters;
 };
 
+// ---- pooled persistent kernel (rtb_pool.cuh) -----------------------------------------------------
+struct PoolParams {
+    DScene scene;
+    DCamera cam;
+    DRender rd;
+    int width, height;
+    int time_ms, frame_num;
+    const float *prev;
+    float *out;
+    int shard_rank, shard_world, band_rows, local_rows;
+    int refill, walk_min;
+    float4 *pool;                 // 6 planes of 64 float4 per warp of the grid
+    unsigned int *work_counter;   // zeroed before launch
+    unsigned long long *counters;
+};
+
 struct LaunchConfig {
     int blocks, threads;
 };
@@ -72,6 +88,9 @@ struct LaunchConfig {
     cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
     cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \
     cudaError_t launch_wf_rebuild(int slot_base, int n_slots, const unsigned char *alive, int *block_count, int *queue, unsigned int *total, cudaStream_t st); \
+    cudaError_t launch_pool(const PoolParams &p, bool brute, bool count, int blocks, cudaStream_t st);              \
+    cudaError_t pool_occupancy(int *blocks_per_sm);                                                                 \
+    int pool_block_threads();                                                                                       \
     }
 RTB_DECLARE_VARIANT(fast)
 RTB_DECLARE_VARIANT(strict)

@@ -82,12 +82,18 @@ __device__ __forceinline__ void ray_finalise(Ray &r, bool aa, uint32_t &rng) {
 }
 
 // Ray::reflect, ray.cu:67-75 with diffuse_reflect :157-170, true_lambertian_reflect :172-178,
-// perfect_reflect :180-186, lerp :32-34
+// perfect_reflect :180-186, lerp :32-34.  The three Box-Muller draws (logf + cosf each) run as a
+// rolled loop and the function has ONE call site (path_shade): the shading code is the larger half
+// of the instruction footprint, and the SM's instruction cache (32 KB) is what the kernels that
+// hold both shading and traversal run out of first.
 __device__ __forceinline__ void reflect(Ray &r, const Surface &sf, float smoothness, uint32_t &rng) {
-    float dx = rng_normal(rng);
-    float dy = rng_normal(rng);
-    float dz = rng_normal(rng);
-    V3 rv = v3(dx, dy, dz);
+    float g0 = 0, g1 = 0, g2 = 0;  // draw order x, y, z (ray.cu:159-161): g2 ends up holding the first draw
+#pragma unroll 1
+    for (int k = 0; k < 3; k++) {
+        g2 = g1; g1 = g0;
+        g0 = rng_normal(rng);
+    }
+    V3 rv = v3(g2, g1, g0);
     if (dot(rv, sf.normal) < 0) rv = rv * -1.f;
     rv = normalised(rv);
     V3 diffuse = normalised(sf.normal + rv);
@@ -97,8 +103,10 @@ __device__ __forceinline__ void reflect(Ray &r, const Surface &sf, float smoothn
     r.d = normalised(diffuse + (spec - diffuse) * smoothness);  // direction_inv: see ray_finalise
 }
 
-// Ray::refract, ray.cu:77-128 + get_reflection_coeff :188-196
-static __device__ __noinline__ void refract(Ray &r, const Surface &sf, float mat_n, float smoothness, float &cur_n, uint32_t &rng) {
+// Ray::refract, ray.cu:77-128 + get_reflection_coeff :188-196.  Returns true when the ray reflects instead
+// (past the critical angle, or the Schlick coefficient wins the draw): the caller then runs reflect(), exactly
+// where the reference calls it (ray.cu:108-111), so the draw order is unchanged.
+static __device__ __noinline__ bool refract(Ray &r, const Surface &sf, float mat_n, float &cur_n, uint32_t &rng) {
     float n1, n2;
     V3 refn;
     if (dot(sf.normal, r.d) > 0) {
@@ -114,16 +122,14 @@ static __device__ __noinline__ void refract(Ray &r, const Surface &sf, float mat
     float r0 = sqrt_r0 * sqrt_r0;
     float cos_theta = cos(theta1);
     float coeff = r0 + (1 - r0) * pow((1 - cos_theta), 5);
-    if (theta1 > critical || coeff > rng_next(rng)) {
-        reflect(r, sf, smoothness, rng);
-        return;
-    }
+    if (theta1 > critical || coeff > rng_next(rng)) return true;
     V3 perp;
     if (theta1 != 0) perp = (r.d - refn * cos(theta1)) / sin(theta1);
     else perp = v3(0, 0, 0);
     V3 res = refn * cos(theta2) + perp * sin(theta2);
     r.o = sf.point;
     r.d = normalised(res);  // direction_inv: see ray_finalise
+    return false;
 }
 
 // Texture::get_texture_colour, material.cu:53-124
@@ -206,8 +212,9 @@ __device__ __forceinline__ bool path_shade(const DScene &s, const FrameConsts &f
         make_surface(s, ray, best, sf);
         const DMaterial &m = s.materials[sf.material];
         int mtype = __ldg(&m.type);
-        if (mtype == 2) refract(ray, sf, __ldg(&m.refractive_index), __ldg(&m.smoothness), P.cur_n, P.rng);
-        else if (mtype == 0 || mtype == 1) reflect(ray, sf, __ldg(&m.smoothness), P.rng);
+        bool reflects = mtype == 0 || mtype == 1;  // update_ray, raytracer.cu:49-64
+        if (mtype == 2) reflects = refract(ray, sf, __ldg(&m.refractive_index), P.cur_n, P.rng);
+        if (reflects) reflect(ray, sf, __ldg(&m.smoothness), P.rng);
         if (mtype == 1) P.col = P.col + v3(__ldg(&m.b[0]), __ldg(&m.b[1]), __ldg(&m.b[2])) * P.thr;
         else P.thr = P.thr * texture_colour(s, m, sf.u, sf.v);
         P.bounce++;
@@ -430,6 +437,7 @@ cudaError_t render_occupancy(int threads, int *blocks_per_sm) {
 }
 
 #include "rtb_wavefront.cuh"
+#include "rtb_pool.cuh"
 
 }  // namespace RTB_NS
 }  // namespace rtb

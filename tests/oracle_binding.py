@@ -6,13 +6,31 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg import this module.
 """
 import ctypes
+import importlib.util
 import os
+import sys
 
 import numpy as np
 
-import raytracer_b200 as rtb
-
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _load_abi():
+    """The ctypes mirror of include/rtb.h (ray-tracer_b200/abi.py), loaded WITHOUT the package around it: importing
+    the package loads librtb.so, and the checkers must also work in processes that may not contain the product
+    (bench.py --impl reference).  Registered under the package's own submodule name, so a later
+    `import raytracer_b200` shares these classes."""
+    name = "raytracer_b200.abi"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "ray-tracer_b200", "abi.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+rtb = _load_abi()  # structure definitions and fixture paths only
 _ORACLE = os.path.join(ROOT, "oracle", "libpt_oracle.so")
 _REF = os.path.join(ROOT, "oracle", "_ref", "libref_host.so")
 NTHREADS = max(1, min(os.cpu_count() or 1, 32))
@@ -45,7 +63,7 @@ class Oracle:
             L.pto_display_rgba8.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
             L.pto_primary_dir.argtypes = [ctypes.POINTER(rtb.CamData), ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
             Oracle.lib = L
-        desc = scene.desc if isinstance(scene, rtb.Scene) else scene
+        desc = scene.desc if hasattr(scene, "desc") else scene
         self._keep = scene
         self.scene = Oracle.lib.pto_scene_create(ctypes.byref(desc))
 
@@ -125,8 +143,9 @@ class RefHost:
         return obj, sub, t
 
 
-def ref_cuda_path(w, h):
-    return os.path.join(ROOT, "baseline", "_ref", f"libref_cuda_{w}x{h}.so")
+def ref_cuda_path(w, h, nofma=False):
+    """the reference's own CUDA build at w x h; nofma = the same sources compiled with -fmad=false (SURVEY.md H2 i)"""
+    return os.path.join(ROOT, "baseline", "_ref", f"libref_cuda_{'nofma_' if nofma else ''}{w}x{h}.so")
 
 
 class RefCuda:
@@ -134,16 +153,16 @@ class RefCuda:
     Process-global state (its three __constant__ symbols)."""
     _libs = {}
 
-    def __init__(self, w, h):
-        path = ref_cuda_path(w, h)
+    def __init__(self, w, h, nofma=False):
+        path = ref_cuda_path(w, h, nofma)
         if not os.path.exists(path):
             raise FileNotFoundError(path)
-        if (w, h) not in RefCuda._libs:
+        if (w, h, nofma) not in RefCuda._libs:
             L = ctypes.CDLL(path)
             L.refc_last_error.restype = ctypes.c_char_p
             L.refc_init.argtypes = [ctypes.c_int] * 3 + [ctypes.c_char_p] + [ctypes.c_int] * 3
-            RefCuda._libs[(w, h)] = L
-        self.L = RefCuda._libs[(w, h)]
+            RefCuda._libs[(w, h, nofma)] = L
+        self.L = RefCuda._libs[(w, h, nofma)]
         self.w, self.h = w, h
         assert self.L.refc_width() == w and self.L.refc_height() == h
 
@@ -170,3 +189,17 @@ class RefCuda:
         if self.L.refc_primary_ids(_p(obj), _p(t)) != 0:
             raise RuntimeError(self.L.refc_last_error().decode())
         return obj, t
+
+    def primary_sub_ids(self, obj):
+        """sub id of every pixel's winning primitive (brute force over a mesh's triangles: small scenes only)"""
+        sub = np.empty((self.h, self.w), np.int32)
+        if self.L.refc_primary_sub_ids(_p(np.ascontiguousarray(obj, np.int32)), _p(sub)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+        return sub
+
+    def count_segments(self, time_ms):
+        """(segments, hit segments) of one frame at the current settings, counted by the reference's own code on the GPU"""
+        seg, hits = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        if self.L.refc_count_segments(time_ms, ctypes.byref(seg), ctypes.byref(hits)) != 0:
+            raise RuntimeError(self.L.refc_last_error().decode())
+        return seg.value, hits.value

@@ -108,13 +108,14 @@ def test_ploc_tree_equals_brute_force(tracer, sid, p0, p1):
 
 @pytest.mark.parametrize("sid,p0,p1", SCENES)
 def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
-    """The wavefront kernels (option kernel=1) evaluate the same per-pixel function with the same
-    RNG order: images, progressive frames and counters are bit-identical to the megakernel's."""
+    """The wavefront kernels (option kernel=1) and the pooled persistent kernel (kernel=3) evaluate the same
+    per-pixel function with the same RNG order: images, progressive frames and counters are bit-identical to
+    the megakernel's."""
     scene = _scene(sid, p0, p1)
     tracer.setup(scene, W, H, 3, 6)
     out = []
     try:
-        for kernel in (0, 1):
+        for kernel in (0, 1, 3):
             tracer.set_option("kernel", kernel)
             tracer.set_option("counters", 1)
             img = np.zeros((H, W, 3), np.float32)
@@ -125,10 +126,11 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
     finally:
         tracer.set_option("kernel", 2)  # library default
         tracer.set_option("counters", 0)
-    assert out[0][1] == out[1][1] == 2
-    assert (out[0][0] == out[1][0]).all()
-    for k in ("segments", "hit_segments", "samples"):
-        assert out[0][2][k] == out[1][2][k]
+    for other in out[1:]:
+        assert out[0][1] == other[1] == 2
+        assert (out[0][0] == other[0]).all()
+        for k in ("segments", "hit_segments", "samples"):
+            assert out[0][2][k] == other[2][k]
 
 
 @pytest.mark.parametrize("groups,streams", [(2, 1), (3, 2), (7, 2)])
@@ -167,24 +169,26 @@ def test_wavefront_sharded_and_odd_sizes(tracer):
     tracer.set_option("kernel", 0)
     tracer.render(full, 0, 99)
     try:
-        tracer.set_option("kernel", 1)
-        combined = np.zeros((Hs, Ws, 3), np.float32)
-        for rank in range(3):
-            tracer.set_shard(rank, 3, 5)
-            part = np.zeros((Hs, Ws, 3), np.float32)
-            tracer.render(part, 0, 99)
-            rows = rtb.shard_rows_host(Hs, rank, 3, 5)
-            combined[rows] = part[rows]
-        tracer.set_shard(0, 1, 8)
-        assert (combined == full).all()
-        # strict-fp variant and zero bounces
+        for kernel in (1, 3):
+            tracer.set_option("kernel", kernel)
+            combined = np.zeros((Hs, Ws, 3), np.float32)
+            for rank in range(3):
+                tracer.set_shard(rank, 3, 5)
+                part = np.zeros((Hs, Ws, 3), np.float32)
+                tracer.render(part, 0, 99)
+                rows = rtb.shard_rows_host(Hs, rank, 3, 5)
+                combined[rows] = part[rows]
+            tracer.set_shard(0, 1, 8)
+            assert (combined == full).all(), f"kernel {kernel}"
+        # strict-fp variant
         tracer.set_option("strict_fp", 1)
-        a = np.zeros((Hs, Ws, 3), np.float32)
-        tracer.render(a, 0, 5)
-        tracer.set_option("kernel", 0)
-        b = np.zeros((Hs, Ws, 3), np.float32)
-        tracer.render(b, 0, 5)
-        assert (a == b).all()
+        imgs = []
+        for kernel in (1, 3, 0):
+            tracer.set_option("kernel", kernel)
+            a = np.zeros((Hs, Ws, 3), np.float32)
+            tracer.render(a, 0, 5)
+            imgs.append(a)
+        assert (imgs[0] == imgs[2]).all() and (imgs[1] == imgs[2]).all()
     finally:
         tracer.set_option("strict_fp", 0)
         tracer.set_option("kernel", 2)  # library default
@@ -350,12 +354,12 @@ def test_far_and_tiny_trees(tracer, scale, z):
                 tracer.set_scene(scene)
                 obj, sub, t = tracer.primary_ids()
                 imgs = []
-                for kernel in (0, 1):
+                for kernel in (0, 1, 3):
                     tracer.set_option("kernel", kernel)
                     img = np.zeros((H, W, 3), np.float32)
                     tracer.render(img, 0, 31)
                     imgs.append(img)
-                assert (imgs[0] == imgs[1]).all()
+                assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[2]).all()
                 results.append((obj, sub, t, imgs[0]))
             assert (results[0][0] >= 0).mean() > 0.2, "the mesh should cover a good part of the frame"
             for a, b in zip(results[0], results[1]):
@@ -384,8 +388,8 @@ def test_auto_kernel_choice(tracer):
             tracer.render(img, 1, 100)
             imgs[kernel] = img
         assert int(tracer.info("kernel_option")) == 2 and int(tracer.info("kernel_tuned")) == 1
-        assert int(tracer.info("kernel")) in (0, 1)
-        assert tracer.info("tune_wavefront_ms") > 0 and tracer.info("tune_megakernel_ms") > 0
+        assert int(tracer.info("kernel")) in (0, 1, 3)
+        assert tracer.info("tune_wavefront_ms") > 0 and tracer.info("tune_megakernel_ms") > 0 and tracer.info("tune_pool_ms") > 0
         assert (imgs[0] == imgs[2]).all()
         # a new resolution tunes again
         tracer.setup(scene, 64, 48, 2, 3)
@@ -468,6 +472,32 @@ def test_edge_cases(tracer):
     assert b"Error from CUDA" in lib.rtb_last_error(tracer.ctx)
 
 
+def test_pool_kernel_edge_cases(tracer):
+    """The pooled persistent kernel on the shapes that stress its slot bookkeeping: fewer pixels than one warp's
+    pool, an image smaller than a tile, zero bounces, an empty scene, a frame whose pixel count is not a multiple
+    of anything -- bit-identical to the megakernel every time."""
+    scene = _scene(4, 60, 7)
+    empty = rtb.SceneDesc()
+    try:
+        for (w, h, spp, bounces, sc) in [(1, 1, 5, 4, scene), (7, 3, 4, 6, scene), (9, 9, 3, 0, scene), (67, 41, 2, 5, scene),
+                                          (33, 17, 3, 4, empty), (130, 67, 1, 1, scene)]:
+            imgs = []
+            for kernel in (0, 3):
+                tracer.set_option("kernel", kernel)
+                tracer.set_camera(rtb.default_camera(w, h), w, h)
+                tracer.set_render_data(scene.render_settings(spp, bounces))
+                tracer.set_scene(sc)
+                img = np.full((h, w, 3), 0.25, np.float32)
+                f = tracer.render(img, 3, 77)
+                tracer.render(img, f, 78)
+                imgs.append(img)
+            assert (imgs[0] == imgs[1]).all(), (w, h, spp, bounces)
+            assert np.isfinite(imgs[0]).all()
+    finally:
+        tracer.set_option("kernel", 2)
+        tracer.setup(scene, 64, 48, 1, 3)
+
+
 def test_bounce_limit_beyond_the_wavefront_packing(tracer):
     """The reference has no upper bound on reflection_limit (src/raytracer.cu:72); the wavefront kernels pack the
     bounce index in 8 bits.  With the automatic kernel choice (the default) a limit of 300 renders through the
@@ -484,9 +514,10 @@ def test_bounce_limit_beyond_the_wavefront_packing(tracer):
             assert int(tracer.info("kernel")) == 0
             imgs[kernel] = img
         assert (imgs[0] == imgs[2]).all() and np.isfinite(imgs[0]).all()
-        tracer.set_option("kernel", 1)
-        with pytest.raises(Exception, match="Error from CUDA"):
-            tracer.render(np.zeros((48, 64, 3), np.float32), 0, 7)
+        for kernel in (1, 3):
+            tracer.set_option("kernel", kernel)
+            with pytest.raises(Exception, match="Error from CUDA"):
+                tracer.render(np.zeros((48, 64, 3), np.float32), 0, 7)
     finally:
         tracer.set_option("kernel", 2)
         tracer.setup(scene, 64, 48, 1, 3)
