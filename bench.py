@@ -73,6 +73,8 @@ class ClockSampler:
         self.interval_ms = interval_ms
 
     def start(self):
+        if os.environ.get("RTB_BENCH_NO_SAMPLER"):   # diagnostics only: does the nvidia-smi loop perturb the run?
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", str(self.interval_ms),
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -175,7 +177,7 @@ def cpu_baseline_leg(workload, threads):
                       + (" (6x5 instance grid)" if sid == 6 else "")}
 
 
-KERNEL_NAMES = {0: ["render_megakernel"], 1: ["wf_traverse", "wf_shade"], 3: ["pool_render"]}
+KERNEL_NAMES = {0: ["render_megakernel"], 1: ["wf_traverse", "wf_shade"], 3: ["pool_render"], 4: ["stream_render"]}
 
 
 def ncu_traffic(workload, kernel_kind):
@@ -285,7 +287,8 @@ def reference_arm(args):
 
 
 KERNEL_DESC = {0: "persistent megakernel", 1: "wavefront: wf_shade + persistent wf_traverse per path segment",
-               3: "pooled persistent kernel: one launch per frame, per-warp slot pools"}
+               3: "pooled persistent kernel: one launch per frame, per-warp slot pools",
+               4: "streaming kernel: one launch per frame, SMs specialised into shading and traversal roles"}
 
 
 class Job:
@@ -312,43 +315,54 @@ class Job:
         if args.builder is not None:
             tr.set_option("builder", args.builder)
         tr.setup(self.scene, W, H, spp, bounces)
-        if self.tiles:
-            tr.set_shard(rank, world, args.band_rows)
-        self.ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
-        rows_mine, rows_pad = tr.shard_rows()
-        self.dense = self.gathered = self.accum = None
-        with torch.cuda.stream(self.ext):
+        self.exchange_desc = "none"
+        self.exchange_launches = 0
+        if world > 1:
+            # the exchange runs INSIDE the library (rtb_comm.cu) on its own NCCL communicator; torch.distributed is
+            # only the plumbing that carries the 128-byte NCCL id and the CUDA IPC handles between the ranks
+            ids = [rtb.Tracer.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            tr.comm_init(ids[0], world, rank)
             if self.tiles:
-                self.dense = torch.zeros(rows_pad * W * 3, device="cuda", dtype=torch.float32)
-                self.gathered = torch.empty(world * rows_pad * W * 3, device="cuda", dtype=torch.float32)
-            if self.slices:
-                class _Dev:  # the library's accumulation image as a torch tensor (no copy)
-                    __cuda_array_interface__ = {"shape": (H * W * 3,), "typestr": "<f4", "data": (tr.device_image_ptr(), False), "version": 2}
-                self.accum = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
+                tr.set_shard(rank, world, args.band_rows)
+                fused = False
+                if args.exchange != 1:
+                    handles = [None] * world
+                    dist.all_gather_object(handles, tr.peer_export())
+                    try:
+                        tr.peer_open(b"".join(handles), world, rank)
+                        fused = True
+                    except rtb.RtbError:
+                        fused = False
+                    flags = [None] * world
+                    dist.all_gather_object(flags, fused)
+                    fused = all(flags)
+                tr.set_option("exchange", 2 if fused else 1)
+                self.exchange_desc = ("fused into the render kernels: finished pixels are stored into every GPU's image over NVLink peer mappings, "
+                                      "NCCL barrier per frame" if fused else "pack + ncclAllGather + unpack per frame")
+                self.exchange_launches = 0 if fused else 2
+            else:
+                tr.set_option("slices", 1)
+                tr.set_option("exchange", 1)
+                self.exchange_desc = "ncclAllReduce(sum) of the accumulation buffer + scale per step"
+                self.exchange_launches = 1
+        self.ext = torch.cuda.ExternalStream(tr.stream(), device=torch.device("cuda", local_rank))
 
     def sharding_desc(self):
         if self.world == 1:
             return "none"
         if self.tiles:
-            return f"tiles: row-cyclic bands of {self.band_rows} rows of one frame, NCCL all-gather per frame"
-        return (f"sample slices: {self.world} frames of {self.spp} spp per step (one per rank, own time seed), "
-                "NCCL all-reduce of the accumulation buffer per step")
+            return f"tiles: row-cyclic bands of {self.band_rows} rows of one frame; exchange inside the library ({self.exchange_desc})"
+        return (f"sample slices: {self.world} frames of {self.spp} spp per step (one per rank, own time seed); exchange inside the library "
+                f"({self.exchange_desc})")
 
     def exchange(self):
-        """the one exchange step of a frame (on the library's stream); returns the kernels it launched"""
-        if self.tiles:
-            self.tr.shard_pack(self.dense.data_ptr())
-            self.dist.all_gather_into_tensor(self.gathered, self.dense)
-            self.tr.shard_unpack(self.gathered.data_ptr())
-            return 2
-        if self.slices:
-            self.dist.all_reduce(self.accum)      # sum of the ranks' running means ...
-            self.accum.mul_(1.0 / self.world)     # ... -> mean over world x spp samples
-            return 1
-        return 0
+        """the exchange of a frame is part of rtb_render_device / rtb_render; returns OUR kernels it launched"""
+        return self.exchange_launches
 
     def frame_time(self, k):
-        return 1000 + k * (self.world if self.slices else 1) + (self.rank if self.slices else 0)
+        """time0 of step k; in sample-slice mode the library seeds this rank's frame with time0 + rank"""
+        return 1000 + k * (self.world if self.slices else 1)
 
     def barrier(self):
         if self.dist is not None:
@@ -381,9 +395,10 @@ class Job:
         self.tr.render_device(1, self.frame_time(k))
         return self.exchange()
 
-    def timed(self, steps, sample_ms=200, first_k=0):
+    def timed(self, steps, sample_ms=200, first_k=0, sync_each_step=False):
         """`steps` steps bracketed by barrier + synchronize, CUDA events on the library's stream, max over ranks.
-        Returns (ms per step, ms per step of the render kernels alone, launches, clocks of rank 0)."""
+        Returns (ms per step, ms per step of the render kernels alone, launches, clocks of rank 0).
+        sync_each_step: the host waits for every step before it enqueues the next (inside the timed region)."""
         torch = self.torch
         with torch.cuda.stream(self.ext):
             per_frame = int(self.tr.info("launches_per_frame"))
@@ -401,6 +416,8 @@ class Job:
                 self.tr.render_device(1, self.frame_time(first_k + k))
                 kev[k][1].record(self.ext)
                 launches += per_frame + self.exchange()
+                if sync_each_step:
+                    self.tr.sync()
             ev1.record(self.ext)
             self.barrier()
             clocks = sampler.stop() if self.rank == 0 else None
@@ -413,12 +430,15 @@ class Job:
         tr = self.tr
         kind = int(tr.info("kernel"))
         tuned = (f"auto: {KERNEL_DESC[kind].split(':')[0]} kept after timing the variants on a {min(self.spp, 8)}-spp frame "
-                 f"(pooled {tr.info('tune_pool_ms'):.2f} ms, wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
+                 f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
                  if int(tr.info("kernel_tuned")) else "fixed by --kernel")
-        return kind, KERNEL_DESC[kind] + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH"), tuned
+        policy = f", traversal policy walk_min {int(tr.info('walk_min'))} / refill {int(tr.info('wf_refill'))}" if kind != 0 else f", walk_min {int(tr.info('walk_min'))}"
+        return kind, KERNEL_DESC[kind] + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH") + policy, tuned
 
     def close(self):
-        self.dense = self.gathered = self.accum = None
+        if self.world > 1 and self.tiles:
+            self.tr.peer_close()
+        self.barrier()
         self.tr.close()
 
 
@@ -433,8 +453,13 @@ def c4_tiles_record(args, rank, world, local_rank, dist):
         for k in range(3):
             job.device_step(k)
     ms_warm, _, _, _ = job.timed(2)
-    steps = max(5, min(400, int(math.ceil(4000.0 / max(ms_warm, 1e-3)))))   # >= 4 s timed: >= 20 clock samples at 100 ms
-    ms_step, kernel_ms, launches, clocks = job.timed(steps, sample_ms=100)
+    # >= 5 s timed: >= 20 clock samples at 200 ms (a 100 ms nvidia-smi loop slowed the launch-heavy frames by 20 %)
+    steps = max(5, min(600, int(math.ceil(5200.0 / max(ms_warm, 1e-3)))))
+    # The host waits for each step before it enqueues the next (the wait is inside the timed region): with tens of
+    # these 560-launch frames enqueued back to back every frame ran 18 % slower on the device (175 ms instead of 148 ms
+    # at N = 1, measured with and without the clock sampler, with the run-ahead bounded to 1-3 frames or not:
+    # tools/c4_probe.py), while frames the host waits for run at 148 ms for as long as one likes.
+    ms_step, kernel_ms, launches, clocks = job.timed(steps, sample_ms=200, sync_each_step=True)
     kind, kdesc, tuned = job.kernel_desc()
     rec = None
     if rank == 0:
@@ -460,7 +485,8 @@ def main():
     ap.add_argument("--ref-spp", type=int, default=0, help="spp per step of the reference arm (0 = the workload's own where a step stays under ~10 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c4-tiles", action="store_true", help="skip the C4 screen-tile record that rides along with the C3 headline")
-    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel, 2 = timed choice (library default)")
+    ap.add_argument("--exchange", type=int, default=2, help="tiles at N > 1: 2 = fused peer-store exchange (falls back to 1 without peer access), 1 = NCCL all-gather")
+    ap.add_argument("--kernel", type=int, default=None, help="0 = persistent megakernel, 1 = wavefront, 3 = pooled, 4 = streaming, 2 = timed choice (library default)")
     ap.add_argument("--builder", type=int, default=None, help="0 = Karras LBVH, 1 = PLOC (library default)")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -508,11 +534,7 @@ def main():
                 tr.render(himg, 0, 1000 + k)  # H2D + kernel + D2H + sync
             else:
                 himg[:] = 0
-                tr.set_accumulation(himg, 0)  # H2D
-                tr.render_device(1, job.frame_time(k))
-                job.exchange()
-                out, _ = tr.download()  # D2H + sync
-                himg[:] = out.reshape(-1)
+                tr.render(himg, 0, job.frame_time(k))  # H2D + kernel + exchange + D2H + sync, every rank gets the image
 
         e2e_step(0)
         job.barrier()

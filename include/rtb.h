@@ -125,6 +125,9 @@ typedef struct rtb_ctx rtb_ctx;
 
 /* ---- lifetime -------------------------------------------------------------------------- */
 int rtb_abi_version(void);
+/* 1 when the library was built with -DRTB_CHECKS (device-side asserts on every queue / slot / stack / node index:
+ * the checked build the GPU tests run once, ray-tracer_b200/librtb_checks.so), else 0 */
+int rtb_build_has_checks(void);
 /* one context per CUDA device (one process per GPU); fails if the device cannot be used */
 int rtb_create(rtb_ctx **out, int device);
 void rtb_destroy(rtb_ctx *ctx);
@@ -211,6 +214,36 @@ int rtb_shard_row_count(int height, int rank, int world, int band_rows);
 int rtb_shard_pack(rtb_ctx *ctx, void *dense_dev);
 int rtb_shard_unpack(rtb_ctx *ctx, const void *gathered_dev);
 
+/* ---- multi-GPU behind the C ABI -------------------------------------------------
+ * The reference is single-device (src/dispatch.cu:127-153); its render(VariableRenderData*, int) has no
+ * counterpart for several GPUs, so these entry points are the extension a maintainer binds next to
+ * render().  NCCL (libnccl.so.2) is loaded at first use.  Two ways to a communicator:
+ *   one process per GPU:  rank 0 calls rtb_comm_unique_id, the 128 bytes reach the other ranks through the
+ *                         caller's own launcher (MPI, torchrun, a file), every rank calls rtb_comm_init;
+ *   one process, n GPUs:  rtb_create_multi (ncclCommInitAll), then rtb_render_multi.
+ * With a communicator, rtb_set_shard(rank, world, band_rows) and option "exchange" != 0, rtb_render /
+ * rtb_render_device complete the image on every rank themselves, on the context's stream:
+ *   "exchange" = 1  tiles: pack -> ncclAllGather -> unpack;  with option "slices" = 1 (sample slices: no shard,
+ *                   frame k of rank r seeded time0 + (k * world + r) * step): ncclAllReduce(sum) + scale;
+ *   "exchange" = 2  tiles with the exchange fused into the render kernels: every finished pixel is stored into
+ *                   all ranks' accumulation images through peer mappings (rtb_peer_export / rtb_peer_open, or
+ *                   direct peer access under rtb_create_multi), the frame ends with a barrier instead of a gather.
+ * At most 8 ranks (one NVSwitch domain). */
+int rtb_comm_unique_id(unsigned char id_out[128]);
+int rtb_comm_init(rtb_ctx *ctx, const unsigned char id[128], int world, int rank);
+int rtb_comm_info(rtb_ctx *ctx, int *world, int *rank);
+/* CUDA IPC handle (64 bytes) of this context's accumulation image / map all ranks' images (world x 64 bytes,
+ * rank order; the entry of `rank` itself is ignored).  The resolution must be set first (rtb_set_camera). */
+int rtb_peer_export(rtb_ctx *ctx, unsigned char handle_out[64]);
+int rtb_peer_open(rtb_ctx *ctx, const unsigned char *handles, int world, int rank);
+int rtb_peer_close(rtb_ctx *ctx);
+/* n contexts on n devices of this process, one communicator, shards preset to (i, n, 8 rows); peer access enabled
+ * where the devices allow it.  Scene, camera and settings are given to every context. */
+int rtb_create_multi(rtb_ctx **ctxs_out, const int *devices, int n);
+/* == render(VariableRenderData*, int) on the n GPUs of rtb_create_multi: host image in / out like rtb_render */
+int rtb_render_multi(rtb_ctx **ctxs, int n, float *rgb_inout, int *frame_num_inout, int current_time_ms);
+void rtb_destroy_multi(rtb_ctx **ctxs, int n);
+
 /* ---- introspection ----------------------------------------------------------------------- */
 /* primary-hit ids with antialias off: obj_id = object index accepted by the
  * reference's `<=` rule or -1; sub_id = triangle inside it (mesh: triangle index; quad 0/1;
@@ -219,13 +252,15 @@ int rtb_primary_ids(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
 /* counters of the last render when option "counters" = 1 */
 int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
 /* options: "counters" 0/1; "traversal" 0 = LBVH, 1 = brute force over the flattened primitives;
- * "kernel" 0 = persistent megakernel, 1 = wavefront, 2 = timed choice between the two at the first frame
- * (default; bit-identical images; beyond the wavefront kernels' packing limits -- reflection_limit > 255 or
- * rays_per_pixel >= 2^24 -- the choice is the megakernel, while "kernel" = 1 refuses such a frame);
+ * "kernel" 0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel (one launch per frame, per-warp
+ * pools of 64 pixel slots), 2 = timed choice between them at the first frame (default; bit-identical images;
+ * beyond the packing limits of kernels 1 and 3 -- reflection_limit > 255 or rays_per_pixel >= 2^24 -- the choice
+ * is the megakernel, while pinning 1 or 3 refuses such a frame);
  * "strict_fp" 0/1 (kernels built with -fmad=false); "builder" 0 = Karras LBVH, 1 = PLOC (next commit);
  * "large_split", "max_large", "reference_bvh_quirks" (next commit); "walk_min", "refill", "wf_refill",
  * "wf_rebuild", "wf_groups", "wf_streams" (traversal / wavefront policy, 0 = tuned); "block_threads";
- * "blocks_per_sm".  Every change re-arms the timed choice. */
+ * "blocks_per_sm"; "tune_set" (kernels the timed choice tries: 1 megakernel | 2 wavefront | 8 pooled);
+ * "exchange" 0/1/2 and "slices" 0/1 (multi-GPU section above).  Every change re-arms the timed choice. */
 int rtb_set_option(rtb_ctx *ctx, const char *key, int value);
 int rtb_get_info(rtb_ctx *ctx, const char *key, double *value);
 /* sustained FP32 FMA throughput of the device (TFLOP/s, dependent-chain FFMA microbenchmark over

@@ -85,6 +85,16 @@ lib.rtb_counters.argtypes = [_vp, ctypes.POINTER(Counters)]
 lib.rtb_set_option.argtypes = [_vp, ctypes.c_char_p, _i]
 lib.rtb_get_info.argtypes = [_vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
 lib.rtb_measure_fp32_peak.argtypes = [_vp, ctypes.c_double, ctypes.POINTER(ctypes.c_double)]
+lib.rtb_comm_unique_id.argtypes = [_vp]
+lib.rtb_comm_init.argtypes = [_vp, _vp, _i, _i]
+lib.rtb_comm_info.argtypes = [_vp, _ip, _ip]
+lib.rtb_peer_export.argtypes = [_vp, _vp]
+lib.rtb_peer_open.argtypes = [_vp, _vp, _i, _i]
+lib.rtb_peer_close.argtypes = [_vp]
+lib.rtb_create_multi.argtypes = [ctypes.POINTER(_vp), _ip, _i]
+lib.rtb_render_multi.argtypes = [ctypes.POINTER(_vp), _i, _vp, _ip, _i]
+lib.rtb_destroy_multi.argtypes = [ctypes.POINTER(_vp), _i]
+lib.rtb_destroy_multi.restype = None
 
 scenes_lib.rtbs_build.restype = _vp
 scenes_lib.rtbs_build.argtypes = [_i, _i, _i, ctypes.c_char_p]
@@ -174,9 +184,12 @@ def _ptr(a):
 class Tracer:
     """One rendering context on one CUDA device (rtb_ctx)."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, _ctx=None):
         self.ctx = ctypes.c_void_p()
-        if lib.rtb_create(ctypes.byref(self.ctx), device) != 0:
+        self._owned = _ctx is None
+        if _ctx is not None:
+            self.ctx = _ctx
+        elif lib.rtb_create(ctypes.byref(self.ctx), device) != 0:
             msg = lib.rtb_last_error(None).decode()
             self.ctx = None
             raise RtbError(msg)
@@ -187,9 +200,34 @@ class Tracer:
             raise RtbError(lib.rtb_last_error(self.ctx).decode())
 
     def close(self):
-        if self.ctx:
+        if self.ctx and self._owned:
             lib.rtb_destroy(self.ctx)
-            self.ctx = None
+        self.ctx = None
+
+    # ---- multi-GPU: one process per GPU (the 128-byte id travels over the caller's own launcher) ----
+    @staticmethod
+    def comm_unique_id():
+        buf = (ctypes.c_ubyte * 128)()
+        if lib.rtb_comm_unique_id(buf) != 0:
+            raise RtbError(lib.rtb_last_error(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, unique_id, world, rank):
+        buf = (ctypes.c_ubyte * 128).from_buffer_copy(unique_id)
+        self._check(lib.rtb_comm_init(self.ctx, buf, world, rank))
+
+    def peer_export(self):
+        buf = (ctypes.c_ubyte * 64)()
+        self._check(lib.rtb_peer_export(self.ctx, buf))
+        return bytes(buf)
+
+    def peer_open(self, handles, world, rank):
+        """handles: world x 64 bytes in rank order (rtb_peer_export of every rank)"""
+        buf = (ctypes.c_ubyte * (64 * world)).from_buffer_copy(handles)
+        self._check(lib.rtb_peer_open(self.ctx, buf, world, rank))
+
+    def peer_close(self):
+        self._check(lib.rtb_peer_close(self.ctx))
 
     def __del__(self):
         self.close()
@@ -317,6 +355,46 @@ class Tracer:
         c = Counters()
         self._check(lib.rtb_counters(self.ctx, ctypes.byref(c)))
         return c.as_dict()
+
+
+class MultiTracer:
+    """n rendering contexts on n CUDA devices of THIS process with one NCCL communicator (rtb_create_multi);
+    render() is the n-GPU form of render(VariableRenderData*, int)."""
+
+    def __init__(self, devices):
+        self.n = len(devices)
+        self._ctxs = (ctypes.c_void_p * self.n)()
+        devs = (ctypes.c_int * self.n)(*devices)
+        if lib.rtb_create_multi(self._ctxs, devs, self.n) != 0:
+            raise RtbError(lib.rtb_last_error(None).decode())
+        self.tracers = [Tracer(_ctx=ctypes.c_void_p(self._ctxs[i])) for i in range(self.n)]
+
+    def setup(self, scene, width, height, spp, bounces, antialias=True):
+        for t in self.tracers:
+            t.setup(scene, width, height, spp, bounces, antialias)
+        self.width, self.height = width, height
+        return self
+
+    def set_option(self, key, value):
+        for t in self.tracers:
+            t.set_option(key, value)
+
+    def render(self, image, frame_num, time_ms):
+        assert image.dtype == np.float32 and image.size == self.width * self.height * 3 and image.flags.c_contiguous
+        f = ctypes.c_int(frame_num)
+        if lib.rtb_render_multi(self._ctxs, self.n, _ptr(image), ctypes.byref(f), time_ms) != 0:
+            raise RtbError(lib.rtb_last_error(self._ctxs[0]).decode())
+        return f.value
+
+    def close(self):
+        if self._ctxs is not None:
+            for t in self.tracers:
+                t.ctx = None
+            lib.rtb_destroy_multi(self._ctxs, self.n)
+            self._ctxs = None
+
+    def __del__(self):
+        self.close()
 
 
 def shard_rows_host(height, rank, world, band_rows):

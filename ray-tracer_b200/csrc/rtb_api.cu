@@ -3,8 +3,7 @@
 // GPU LBVH build, persistent device buffers, render entry points.  Replaces src/dispatch.cu of the
 // reference (per-frame cudaMalloc/cudaMallocManaged/cudaFree, element-wise managed-memory copy out,
 // three __constant__ symbols).  No CPU fallback: every entry point needs a working CUDA device.
-#include "../../include/rtb.h"
-#include "rtb_launch.h"
+#include "rtb_ctx.h"
 #include "rtb_lbvh.h"
 #include "rtb_refbvh.h"
 
@@ -18,115 +17,12 @@
 #include <utility>
 #include <vector>
 
-using namespace rtb;
-
-namespace {
-std::string g_create_error;
+std::string &rtb_create_error() {
+    static std::string e;
+    return e;
 }
 
-struct rtb_ctx {
-    int device = 0;
-    int num_sms = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    std::string err;
-
-    int width = 0, height = 0;
-    bool have_cam = false, have_rd = false;
-    RtbCamData cam{};
-    RtbRenderData rd{};
-
-    // host-side scene description (owned copies)
-    std::vector<RtbObject> objects;
-    std::vector<RtbMaterial> materials;
-    std::vector<float> tri_points, tri_uv;
-    std::vector<std::vector<float>> image_data;
-    std::vector<RtbImage> images;
-    bool committed = false;
-
-    // device scene
-    DScene d{};
-    std::vector<void *> scene_allocs;
-    double build_ms = 0, commit_ms = 0;  // device time of the tree build / wall time of the whole commit
-    size_t scene_bytes = 0;
-    int culled_tris = 0;
-
-    // frame state
-    float *d_image = nullptr;
-    unsigned char *d_rgba = nullptr;  // display conversion buffer (rtb_display_rgba8)
-    size_t rgba_pixels = 0;
-    size_t image_floats = 0;
-    int frame_num = 0;
-    unsigned int *d_work = nullptr;
-    unsigned long long *d_counters = nullptr;
-    RtbCounters last_counters{};
-    unsigned long long last_lane_stats[8] = {};  // traversal lane occupancy of the last counted render (wavefront)
-    bool timing_pending = false;
-
-    // wavefront variant: per-pixel records, two queues, counters {n[0], n[1], fetch}
-    float4 *d_wf_state = nullptr;
-    int *d_wf_queue = nullptr;
-    unsigned char *d_wf_alive = nullptr;
-    int *d_wf_block_count = nullptr;
-    unsigned int *d_wf_counts = nullptr;
-    size_t wf_slots = 0;
-    int wf_shade_per_sm = 0, wf_trav_per_sm = 0;
-    // option "wf_timing": CUDA events around every launch of the next frame (diagnostics only)
-    int opt_wf_timing = 0;
-    int opt_wf_rebuild = 16;  // iterations between queue rebuilds (0 = never)
-    int opt_wf_groups = 2, opt_wf_streams = 2;  // row groups taken through the frame one after the other / concurrent groups
-    cudaStream_t stream2 = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    std::vector<cudaEvent_t> wf_events;
-    size_t wf_events_used = 0;
-    double wf_shade_ms = 0, wf_traverse_ms = 0, wf_total_ms = 0;
-
-    // pooled persistent kernel: per-warp slot records (6 KB per warp of the grid)
-    float4 *d_pool = nullptr;
-    size_t pool_warps = 0;
-    int pool_per_sm = 0;
-
-    // options
-    // 0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel, 2 = auto: the variants are timed on
-    // the first frame after the scene / resolution / settings / shard change and the fastest is kept (bit-identical)
-    int opt_kernel = 2;
-    int auto_choice = -1;                  // -1 = not tuned yet
-    double tune_ms[4] = {0, 0, 0, 0};      // device ms of the tuning frame, by kernel id ([0] megakernel, [1] wavefront, [3] pooled)
-    int tuned_prims = -1;                  // primitive count the choice was tuned on
-    int opt_tune_set = 8 | 2 | 1;          // kernels the timed choice tries: bit k = kernel id k
-    float *d_tune_scratch = nullptr;       // scratch image of the tuning frames (kept: dynamic scenes re-tune)
-    size_t tune_scratch_floats = 0;
-    int opt_counters = 0, opt_traversal = 0, opt_strict = 0, opt_ref_quirks = 1, opt_large_split = 1, opt_max_large = 24, opt_refill = 24;
-    // traversal policy knobs; 0 = automatic: megakernel walk_min 8; wavefront (walk_min, wf_refill) = (16, 8) or (12, 16),
-    // whichever the tuning frame measures faster (closed rooms prefer the second, the 1 M-triangle grid the first)
-    int opt_walk_min = 0, opt_wf_refill = 0;
-    int tuned_walk_min = 16, tuned_refill = 8;
-    int opt_builder = 1, opt_ploc_radius = 16;  // 0 = Karras LBVH, 1 = PLOC; take effect at the next commit
-    int opt_threads = RTB_BLOCK_THREADS, opt_blocks_per_sm = 0;
-    int shard_rank = 0, shard_world = 1, band_rows = 8;
-};
-
 namespace {
-
-int fail(rtb_ctx *ctx, const char *where, const char *msg) {
-    std::string s = std::string("Error from CUDA (") + where + "): " + msg;  // check_cuda_error shape, utils.cu:5-10
-    if (ctx) ctx->err = s; else g_create_error = s;
-    return 1;
-}
-
-#define RTB_CUDA(ctx, call, where)                                           \
-    do {                                                                     \
-        cudaError_t e_ = (call);                                             \
-        if (e_ != cudaSuccess) return fail(ctx, where, cudaGetErrorString(e_)); \
-    } while (0)
-
-struct Bind {  // make ctx's device current for the duration of a call
-    int prev = -1;
-    explicit Bind(rtb_ctx *c) {
-        cudaGetDevice(&prev);
-        if (prev != c->device) cudaSetDevice(c->device);
-    }
-};
 
 void free_scene(rtb_ctx *c) {
     for (void *p : c->scene_allocs) cudaFree(p);
@@ -256,6 +152,75 @@ struct Flat {
         note_box(blo, bhi);
     }
 };
+
+// ---- EXPERIMENT: full-sweep SAH, top-down, one primitive per leaf, on the host -------------------------------
+struct SahBox {
+    float lo[3], hi[3];
+    void grow(const float *b) { for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], b[k]); hi[k] = std::max(hi[k], b[3 + k]); } }
+    void grow(const SahBox &o) { for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], o.lo[k]); hi[k] = std::max(hi[k], o.hi[k]); } }
+    float area() const { float e0 = hi[0] - lo[0], e1 = hi[1] - lo[1], e2 = hi[2] - lo[2]; return e0 * e1 + e1 * e2 + e2 * e0; }
+    static SahBox empty() { return SahBox{{3e38f, 3e38f, 3e38f}, {-3e38f, -3e38f, -3e38f}}; }
+};
+
+void sah_pad(const SahBox &b, int ref, float4 &olo, float4 &ohi) {  // the padding of rtb_lbvh.cu padded()
+    float p[3];
+    for (int k = 0; k < 3; k++) p[k] = 4e-7f * fmaxf(fmaxf(fabsf(b.lo[k]), fabsf(b.hi[k])), b.hi[k] - b.lo[k]) + 1e-12f;
+    olo = make_float4(b.lo[0] - p[0], b.lo[1] - p[1], b.lo[2] - p[2], 0.f);
+    std::memcpy(&olo.w, &ref, sizeof(int));
+    ohi = make_float4(b.hi[0] + p[0], b.hi[1] + p[1], b.hi[2] + p[2], 0.f);
+}
+
+// builds the subtree over prims[first, first + n) (n >= 2) as node `self`; returns its box
+SahBox sah_build_rec(const std::vector<float> &leaf_box, const std::vector<int> &idx, const std::vector<int> &refs, std::vector<int> &prims,
+                     int first, int n, std::vector<float4> &nodes, int self, int depth, int &height) {
+    if (depth > height) height = depth;
+    auto box_of = [&](int prim) { const float *b = &leaf_box[6 * (size_t)idx[prim]]; SahBox r = SahBox::empty(); r.grow(b); return r; };
+    int best_axis = 0, best_split = n / 2;
+    float best_cost = 3e38f;
+    std::vector<float> right_area(n);
+    std::vector<int> order(prims.begin() + first, prims.begin() + first + n), best_order;
+    for (int axis = 0; axis < 3; axis++) {
+        std::sort(order.begin(), order.end(), [&](int a, int b) {
+            const float *ba = &leaf_box[6 * (size_t)idx[a]], *bb = &leaf_box[6 * (size_t)idx[b]];
+            float ca = ba[axis] + ba[3 + axis], cb = bb[axis] + bb[3 + axis];
+            return ca < cb || (ca == cb && a < b);
+        });
+        SahBox acc = SahBox::empty();
+        for (int i = n - 1; i > 0; i--) { acc.grow(box_of(order[i])); right_area[i] = acc.area(); }
+        acc = SahBox::empty();
+        for (int i = 1; i < n; i++) {
+            acc.grow(box_of(order[i - 1]));
+            float cost = acc.area() * i + right_area[i] * (n - i);
+            if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i; best_order = order; }
+        }
+    }
+    (void)best_axis;
+    if (best_order.empty()) best_order = order;
+    std::copy(best_order.begin(), best_order.end(), prims.begin() + first);
+    int nl = best_split, nr = n - best_split;
+    SahBox bl, br;
+    int refl, refr;
+    if (nl == 1) { bl = box_of(prims[first]); refl = refs[prims[first]]; }
+    else { refl = (int)(nodes.size() / 4); nodes.resize(nodes.size() + 4); bl = sah_build_rec(leaf_box, idx, refs, prims, first, nl, nodes, refl, depth + 1, height); }
+    if (nr == 1) { br = box_of(prims[first + nl]); refr = refs[prims[first + nl]]; }
+    else { refr = (int)(nodes.size() / 4); nodes.resize(nodes.size() + 4); br = sah_build_rec(leaf_box, idx, refs, prims, first + nl, nr, nodes, refr, depth + 1, height); }
+    float4 a, b2, c2, d2;
+    sah_pad(bl, refl, a, b2);
+    sah_pad(br, refr, c2, d2);
+    nodes[4 * (size_t)self] = a; nodes[4 * (size_t)self + 1] = b2; nodes[4 * (size_t)self + 2] = c2; nodes[4 * (size_t)self + 3] = d2;
+    SahBox all = bl;
+    all.grow(br);
+    return all;
+}
+
+int sah_build_host(const std::vector<float> &leaf_box, const std::vector<int> &idx, const std::vector<int> &refs, std::vector<float4> &nodes) {
+    int n = (int)refs.size(), height = 0;
+    std::vector<int> prims(n);
+    for (int i = 0; i < n; i++) prims[i] = i;
+    nodes.assign(4, make_float4(0, 0, 0, 0));
+    sah_build_rec(leaf_box, idx, refs, prims, 0, n, nodes, 0, 1, height);
+    return height;
+}
 
 int flatten(rtb_ctx *c, Flat &f) {
     // image store -> one float array
@@ -446,8 +411,13 @@ int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num);
 
 int launch_frame_pool(rtb_ctx *c, int time_ms, int frame_num);
 
+int launch_frame_stream(rtb_ctx *c, int time_ms, int frame_num);
+
+int check_stream_watchdog(rtb_ctx *c);
+
 int launch_kernel_variant(rtb_ctx *c, int kern, int time_ms, int frame_num) {
-    return kern == 1 ? launch_frame_wavefront(c, time_ms, frame_num) : kern == 3 ? launch_frame_pool(c, time_ms, frame_num) : launch_frame_megakernel(c, time_ms, frame_num);
+    return kern == 1 ? launch_frame_wavefront(c, time_ms, frame_num) : kern == 3 ? launch_frame_pool(c, time_ms, frame_num)
+         : kern == 4 ? launch_frame_stream(c, time_ms, frame_num) : launch_frame_megakernel(c, time_ms, frame_num);
 }
 
 // option "kernel" = 2: a short frame (RTB_TUNE_SPP samples per pixel of the real scene, camera, shard
@@ -463,14 +433,14 @@ bool wavefront_fits(const rtb_ctx *c) { return c->rd.reflection_limit <= 255 && 
 int autotune_kernel(rtb_ctx *c) {
     c->tuned_prims = c->d.num_prims;
     if (!wavefront_fits(c)) { c->auto_choice = 0; return 0; }
-    c->auto_choice = 3;
+    c->auto_choice = 1;
     if (c->opt_counters || c->image_floats == 0) return 0;  // counted builds are not timed
     if (c->tune_scratch_floats != c->image_floats) {
         if (c->d_tune_scratch) cudaFree(c->d_tune_scratch);
         c->d_tune_scratch = nullptr; c->tune_scratch_floats = 0;
         if (cudaMalloc((void **)&c->d_tune_scratch, c->image_floats * sizeof(float)) != cudaSuccess) {
             cudaGetLastError();
-            return 0;  // no room for a scratch image: keep the pooled kernel
+            return 0;  // no room for a scratch image: keep the wavefront kernels
         }
         c->tune_scratch_floats = c->image_floats;
     }
@@ -484,6 +454,7 @@ int autotune_kernel(rtb_ctx *c) {
     // candidates: each kernel with its traversal policies (walk_min, refill); the megakernel has one
     struct Cand { int kern, walk_min, refill; float ms; };
     std::vector<Cand> cand;
+    if (c->opt_tune_set & 16) { cand.push_back({4, 16, 8, 0.f}); cand.push_back({4, 12, 16, 0.f}); }
     if (c->opt_tune_set & 8) { cand.push_back({3, 16, 8, 0.f}); cand.push_back({3, 12, 16, 0.f}); }
     if (c->opt_tune_set & 2) { cand.push_back({1, 16, 8, 0.f}); cand.push_back({1, 12, 16, 0.f}); }
     if (c->opt_tune_set & 1) cand.push_back({0, 0, 0, 0.f});
@@ -493,8 +464,17 @@ int autotune_kernel(rtb_ctx *c) {
         const bool second_policy = i > 0 && cand[i - 1].kern == cand[i].kern;
         if (second_policy && pinned) { cand[i].ms = 1e30f; continue; }
         c->tuned_walk_min = cand[i].walk_min; c->tuned_refill = cand[i].refill;
-        for (int pass = (warmed >> cand[i].kern) & 1; pass < 2 && rc == 0; pass++) {  // pass 0 warms the kernels up at 1 spp
-            c->rd.rays_per_pixel = pass == 0 ? 1 : std::min(rd.rays_per_pixel, RTB_TUNE_SPP);
+        // pass plan: a 1-spp frame warms a kernel up the first time it runs, then the timed frame.  The streaming
+        // kernel balances its SM split from the utilisation the previous frame measured: two more short frames
+        // let it settle before the timed one.
+        std::vector<int> plan;
+        if (!((warmed >> cand[i].kern) & 1)) {
+            plan.push_back(1);
+            if (cand[i].kern == 4) { plan.push_back(4); plan.push_back(4); }
+        }
+        plan.push_back(RTB_TUNE_SPP);
+        for (size_t pass = 0; pass < plan.size() && rc == 0; pass++) {
+            c->rd.rays_per_pixel = std::min(rd.rays_per_pixel, plan[pass]);
             cudaMemsetAsync(scratch, 0, c->image_floats * sizeof(float), c->stream);
             cudaEventRecord(e0, c->stream);
             rc = launch_kernel_variant(c, cand[i].kern, 12345, 0);
@@ -509,8 +489,8 @@ int autotune_kernel(rtb_ctx *c) {
     c->rd = rd;
     c->d_image = image;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    if (rc != 0 || cand.empty()) { c->auto_choice = rc != 0 ? -1 : 3; return rc; }
-    for (int k = 0; k < 4; k++) c->tune_ms[k] = 0;
+    if (rc != 0 || cand.empty()) { c->auto_choice = rc != 0 ? -1 : 1; return rc; }
+    for (int k = 0; k < 5; k++) c->tune_ms[k] = 0;
     size_t best = 0;
     for (size_t i = 0; i < cand.size(); i++) {
         if (cand[i].ms < cand[best].ms) best = i;
@@ -522,11 +502,131 @@ int autotune_kernel(rtb_ctx *c) {
     return 0;
 }
 
-int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? (wavefront_fits(c) ? 3 : 0) : c->auto_choice) : c->opt_kernel; }
+int effective_kernel(const rtb_ctx *c) { return c->opt_kernel == 2 ? (c->auto_choice < 0 ? (wavefront_fits(c) ? 1 : 0) : c->auto_choice) : c->opt_kernel; }
 
 int launch_frame(rtb_ctx *c, int time_ms, int frame_num) {
     if (c->opt_kernel == 2 && c->auto_choice < 0 && autotune_kernel(c) != 0) return 1;
     return launch_kernel_variant(c, effective_kernel(c), time_ms, frame_num);
+}
+
+// One frame through the streaming kernel (rtb_stream.cuh): one launch; the SM split follows the utilisation the
+// previous frame measured (shade work ~ shade SMs x busy fraction, likewise traversal).
+int launch_frame_stream(rtb_ctx *c, int time_ms, int frame_num) {
+    if (!wavefront_fits(c) || c->width > 65535 || c->height > 65535)
+        return fail(c, "render", "the streaming kernel packs the bounce index in 8 bits, the sample index in 24 and a pixel coordinate in 16 "
+                                 "(reflection_limit <= 255, rays_per_pixel < 2^24, width and height < 65536): use option kernel = 0 or 2");
+    const bool strict_fp = c->opt_strict != 0;
+    const int local_rows = shard_local_rows(c, c->shard_rank);
+    const size_t pixels = (size_t)c->width * local_rows;
+    if (pixels == 0) return 0;
+    if (c->stream_per_sm == 0) {
+        cudaError_t e = strict_fp ? strict::stream_occupancy(&c->stream_per_sm) : fast::stream_occupancy(&c->stream_per_sm);
+        if (e != cudaSuccess || c->stream_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
+    }
+    const int threads = strict_fp ? strict::stream_block_threads() : fast::stream_block_threads();
+    int per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->stream_per_sm) : c->stream_per_sm;
+    const int blocks = c->num_sms * per_sm;
+    // slots in flight: enough to keep every lane of both roles busy with queue slack, few enough to stay in the L2
+    size_t want_slots = std::min(pixels, (size_t)c->num_sms * 1024 * (size_t)std::max(1, c->opt_stream_slots));
+    want_slots = std::max<size_t>(want_slots, 32);
+    // ring entries per sub-queue: a power of two, at least the slot count (a slot sits in at most one queue) and large
+    // enough that the tickets drawn ahead of the tail (at most one per lane of the grid) stay within one lap
+    size_t cap = (size_t)1 << 18;
+    while (cap < want_slots) cap <<= 1;
+    const int NQ = RTB_STREAM_SHARDS;
+    const size_t ctl_words = 8 + 2 * 2 * NQ * 32 + 1024 + 8;   // ctl, head/tail of two queues (NQ sub-queues, 32 words apart), sm_role, stats (4 x u64)
+    if (c->stream_slots < want_slots || c->stream_cap < cap) {
+        if (c->d_stream_state) cudaFree(c->d_stream_state);
+        if (c->d_stream_pix) cudaFree(c->d_stream_pix);
+        if (c->d_stream_rings) cudaFree(c->d_stream_rings);
+        c->d_stream_state = nullptr; c->d_stream_pix = nullptr; c->d_stream_rings = nullptr; c->stream_slots = 0; c->stream_cap = 0;
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_stream_state, want_slots * 6 * sizeof(float4)), "allocating the slot records");
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_stream_pix, want_slots * sizeof(unsigned int)), "allocating the slot records");
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_stream_rings, 2 * NQ * cap * sizeof(int)), "allocating the stream queues");
+        RTB_CUDA(c, cudaMemsetAsync(c->d_stream_rings, 0, 2 * NQ * cap * sizeof(int), c->stream), "clearing the stream queues");
+        c->stream_slots = want_slots; c->stream_cap = cap;
+    }
+    if (!c->d_stream_ctl) RTB_CUDA(c, cudaMalloc((void **)&c->d_stream_ctl, ctl_words * sizeof(unsigned int)), "allocating the stream control block");
+    // the split: the caller's, else the one balanced from the previous frame's utilisation, else 40 % shading
+    int shade_sms = c->opt_stream_shade_sms > 0 ? c->opt_stream_shade_sms : (c->stream_shade_sms > 0 ? c->stream_shade_sms : (c->num_sms * 2 + 2) / 5);
+    shade_sms = std::max(1, std::min(c->num_sms - 1, shade_sms));
+    c->stream_shade_sms = shade_sms;
+    StreamParams p;
+    p.scene = c->d;
+    std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
+    p.rd.rays_per_pixel = c->rd.rays_per_pixel;
+    p.rd.reflection_limit = c->rd.reflection_limit;
+    p.rd.antialias = c->rd.antialias;
+    p.rd.sky[0] = c->rd.sky_colour.x; p.rd.sky[1] = c->rd.sky_colour.y; p.rd.sky[2] = c->rd.sky_colour.z;
+    p.width = c->width; p.height = c->height;
+    p.time_ms = time_ms; p.frame_num = frame_num;
+    p.prev = c->d_image; p.out = c->d_image;
+    p.peers.n = 0;
+    for (int r = 0; r < RTB_MAX_PEERS; r++) p.peers.image[r] = nullptr;
+    if (c->opt_exchange == 2 && !c->opt_slices && c->n_peers == c->shard_world && c->shard_world > 1 && c->d_image == c->peer_image[c->shard_rank]) {
+        p.peers.n = c->n_peers;  // fused exchange: finished pixels go to every GPU's image
+        for (int r = 0; r < c->n_peers; r++) p.peers.image[r] = c->peer_image[r];
+    }
+    p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
+    p.local_rows = local_rows;
+    p.refill = c->opt_wf_refill < 1 ? c->tuned_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
+    p.walk_min = c->opt_walk_min < 1 ? c->tuned_walk_min : (c->opt_walk_min > 32 ? 32 : c->opt_walk_min);
+    const size_t slots = c->stream_slots;
+    float4 *st = c->d_stream_state;
+    p.st.A = st; p.st.B = st + slots; p.st.C = st + 2 * slots; p.st.O = st + 3 * slots; p.st.D = st + 4 * slots; p.st.H = st + 5 * slots;
+    p.pix = c->d_stream_pix;
+    unsigned int *ctl = c->d_stream_ctl;
+    p.ctl = ctl;
+    p.rq.ring = c->d_stream_rings; p.rq.head = ctl + 8; p.rq.tail = ctl + 8 + NQ * 32; p.rq.mask = (unsigned int)(c->stream_cap - 1);
+    p.hq.ring = c->d_stream_rings + NQ * c->stream_cap; p.hq.head = ctl + 8 + 2 * NQ * 32; p.hq.tail = ctl + 8 + 3 * NQ * 32; p.hq.mask = (unsigned int)(c->stream_cap - 1);
+    p.sm_role = (int *)(ctl + 8 + 4 * NQ * 32);
+    p.stats = (unsigned long long *)(ctl + 8 + 4 * NQ * 32 + 1024);
+    p.num_slots = (int)std::min(want_slots, slots);
+    p.total_pixels = (unsigned int)pixels;
+    p.shade_sms = shade_sms; p.total_sms = c->num_sms;
+    p.counters = c->opt_counters ? c->d_counters : nullptr;
+    // the previous frame's utilisation -> the next frame's split (read before the control block is cleared)
+    // (a host round trip: every frame while the split settles, then now and then)
+    if (c->stream_frames_launched > 0 && c->opt_stream_shade_sms <= 0 && (c->stream_frames_launched < 8 || c->stream_frames_launched % 64 == 0)) {
+        unsigned long long h[4];
+        RTB_CUDA(c, cudaMemcpyAsync(h, p.stats, sizeof h, cudaMemcpyDeviceToHost, c->stream), "reading the stream statistics");
+        RTB_CUDA(c, cudaStreamSynchronize(c->stream), "reading the stream statistics");
+        if (h[1] > 0 && h[3] > 0) {
+            double us = (double)h[0] / (double)h[1], ut = (double)h[2] / (double)h[3];
+            c->stream_util[0] = us; c->stream_util[1] = ut;
+            double ws = c->stream_last_shade_sms * us, wt = (c->num_sms - c->stream_last_shade_sms) * ut;
+            if (ws + wt > 0) {
+                int next = (int)std::lround(c->num_sms * ws / (ws + wt));
+                next = std::max(4, std::min(c->num_sms - 4, next));
+                // move towards it (half the way damps the noise of a short frame), never by less than one SM
+                int cur = c->stream_last_shade_sms, step = (next - cur) / 2;
+                if (step == 0 && next != cur) step = next > cur ? 1 : -1;
+                shade_sms = cur + step;
+                c->stream_shade_sms = shade_sms;
+                p.shade_sms = shade_sms;
+            }
+        }
+    }
+    RTB_CUDA(c, cudaMemsetAsync(ctl, 0, ctl_words * sizeof(unsigned int), c->stream), "clearing the stream control block");
+    RTB_CUDA(c, cudaMemsetAsync(c->d_stream_rings, 0, 2 * NQ * c->stream_cap * sizeof(int), c->stream), "clearing the stream queues");
+    cudaError_t e = strict_fp ? strict::launch_stream(p, c->opt_traversal == 1, c->opt_counters != 0, blocks, c->stream)
+                              : fast::launch_stream(p, c->opt_traversal == 1, c->opt_counters != 0, blocks, c->stream);
+    if (e != cudaSuccess) return fail(c, "launching render kernel", cudaGetErrorString(e));
+    c->stream_last_shade_sms = p.shade_sms;
+    c->stream_frames_launched++;
+    // the watchdog word is copied out right behind the kernel (pinned host word, no synchronisation here)
+    if (!c->h_stream_error) RTB_CUDA(c, cudaMallocHost((void **)&c->h_stream_error, sizeof(unsigned int)), "allocating the watchdog word");
+    RTB_CUDA(c, cudaMemcpyAsync(c->h_stream_error, ctl + 5, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream), "reading the watchdog word");
+    c->stream_error_check_pending = true;
+    return 0;
+}
+
+// after a synchronisation: did the streaming kernel's watchdog fire?
+int check_stream_watchdog(rtb_ctx *c) {
+    if (!c->stream_error_check_pending || !c->h_stream_error) return 0;
+    c->stream_error_check_pending = false;
+    if (*c->h_stream_error != 0) return fail(c, "render", "the streaming kernel stalled (its warps waited for each other for seconds): please report; option kernel = 1 renders the same image");
+    return 0;
 }
 
 // One frame through the pooled persistent kernel (rtb_pool.cuh): one launch.
@@ -559,6 +659,12 @@ int launch_frame_pool(rtb_ctx *c, int time_ms, int frame_num) {
     p.width = c->width; p.height = c->height;
     p.time_ms = time_ms; p.frame_num = frame_num;
     p.prev = c->d_image; p.out = c->d_image;
+    p.peers.n = 0;
+    for (int r = 0; r < RTB_MAX_PEERS; r++) p.peers.image[r] = nullptr;
+    if (c->opt_exchange == 2 && !c->opt_slices && c->n_peers == c->shard_world && c->shard_world > 1 && c->d_image == c->peer_image[c->shard_rank]) {
+        p.peers.n = c->n_peers;  // fused exchange: finished pixels go to every GPU's image
+        for (int r = 0; r < c->n_peers; r++) p.peers.image[r] = c->peer_image[r];
+    }
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
     p.refill = c->opt_wf_refill < 1 ? c->tuned_refill : (c->opt_wf_refill > 32 ? 32 : c->opt_wf_refill);
@@ -584,6 +690,12 @@ int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num) {
     p.width = c->width; p.height = c->height;
     p.time_ms = time_ms; p.frame_num = frame_num;
     p.prev = c->d_image; p.out = c->d_image;
+    p.peers.n = 0;
+    for (int r = 0; r < RTB_MAX_PEERS; r++) p.peers.image[r] = nullptr;
+    if (c->opt_exchange == 2 && !c->opt_slices && c->n_peers == c->shard_world && c->shard_world > 1 && c->d_image == c->peer_image[c->shard_rank]) {
+        p.peers.n = c->n_peers;  // fused exchange: finished pixels go to every GPU's image
+        for (int r = 0; r < c->n_peers; r++) p.peers.image[r] = c->peer_image[r];
+    }
     p.shard_rank = c->shard_rank; p.shard_world = c->shard_world; p.band_rows = c->band_rows;
     p.local_rows = shard_local_rows(c, c->shard_rank);
     p.refill = c->opt_refill < 1 ? 1 : (c->opt_refill > 32 ? 32 : c->opt_refill);
@@ -642,6 +754,12 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     base.width = c->width; base.height = c->height;
     base.time_ms = time_ms; base.frame_num = frame_num;
     base.prev = c->d_image; base.out = c->d_image;
+    base.peers.n = 0;
+    for (int r = 0; r < RTB_MAX_PEERS; r++) base.peers.image[r] = nullptr;
+    if (c->opt_exchange == 2 && !c->opt_slices && c->n_peers == c->shard_world && c->shard_world > 1 && c->d_image == c->peer_image[c->shard_rank]) {
+        base.peers.n = c->n_peers;  // fused exchange: finished pixels go to every GPU's image
+        for (int r = 0; r < c->n_peers; r++) base.peers.image[r] = c->peer_image[r];
+    }
     base.shard_rank = c->shard_rank; base.shard_world = c->shard_world; base.band_rows = c->band_rows;
     base.local_rows = local_rows;
     float4 *st = c->d_wf_state;
@@ -766,6 +884,13 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     return 0;
 }
 
+// seed of frame k of a render call.  Sample slices (SURVEY.md 8(e) partitioning B): the ranks render disjoint
+// frames of one progressive sequence, frame f = k * world + rank, seeded time0 + f * step.
+int frame_time(const rtb_ctx *c, int time0_ms, int k, int time_step_ms) {
+    if (c->opt_slices && c->comm && c->comm_world > 1) return time0_ms + (k * c->comm_world + c->comm_rank) * time_step_ms;
+    return time0_ms + k * time_step_ms;
+}
+
 int check_ready(rtb_ctx *c) {
     if (!c) return 1;
     if (!c->have_cam) return fail(c, "render", "camera not set (rtb_set_camera)");
@@ -797,6 +922,14 @@ extern "C" {
 
 int rtb_abi_version(void) { return RTB_ABI_VERSION; }
 
+int rtb_build_has_checks(void) {
+#ifdef RTB_CHECKS
+    return 1;
+#else
+    return 0;
+#endif
+}
+
 int rtb_shard_row_of(int local_row, int rank, int world, int band_rows) {
     if (world <= 1 || band_rows <= 0) return local_row;
     int band = local_row / band_rows, within = local_row - band * band_rows;
@@ -812,7 +945,7 @@ int rtb_shard_row_count(int height, int rank, int world, int band_rows) {
     return full * band_rows + extra;
 }
 
-const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+const char *rtb_last_error(rtb_ctx *ctx) { return ctx ? ctx->err.c_str() : rtb_create_error().c_str(); }
 
 int rtb_create(rtb_ctx **out, int device) {
     if (!out) return fail(nullptr, "rtb_create", "null output pointer");
@@ -821,7 +954,13 @@ int rtb_create(rtb_ctx **out, int device) {
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess) return fail(nullptr, "rtb_create", cudaGetErrorString(e));
     if (device < 0 || device >= count) return fail(nullptr, "rtb_create", "no such CUDA device");
+    int caller_device = -1;
+    if (cudaGetDevice(&caller_device) != cudaSuccess) caller_device = -1;
     RTB_CUDA(nullptr, cudaSetDevice(device), "selecting device");
+    struct Restore {  // the caller's current device is the caller's business
+        int prev, dev;
+        ~Restore() { if (prev >= 0 && prev != dev) cudaSetDevice(prev); }
+    } restore{caller_device, device};
     rtb_ctx *c = new rtb_ctx();
     c->device = device;
     cudaDeviceProp prop;
@@ -846,6 +985,7 @@ void rtb_destroy(rtb_ctx *c) {
     Bind b(c);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
+    rtb_comm_release(c);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_rgba) cudaFree(c->d_rgba);
     if (c->d_work) cudaFree(c->d_work);
@@ -856,6 +996,12 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->d_wf_alive) cudaFree(c->d_wf_alive);
     if (c->d_wf_block_count) cudaFree(c->d_wf_block_count);
     if (c->d_pool) cudaFree(c->d_pool);
+    if (c->d_stream_state) cudaFree(c->d_stream_state);
+    if (c->d_stream_pix) cudaFree(c->d_stream_pix);
+    if (c->d_stream_rings) cudaFree(c->d_stream_rings);
+    for (cudaEvent_t &ev : c->frame_done) if (ev) cudaEventDestroy(ev);
+    if (c->d_stream_ctl) cudaFree(c->d_stream_ctl);
+    if (c->h_stream_error) cudaFreeHost(c->h_stream_error);
     if (c->d_tune_scratch) cudaFree(c->d_tune_scratch);
     for (cudaEvent_t ev : c->wf_events) cudaEventDestroy(ev);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -1023,7 +1169,7 @@ static int scene_commit_timed(rtb_ctx *c) {
     d.num_prims = (int)f.leaf_refs.size();
     // large-primitive split: a leaf whose box area exceeds 1/20 of the scene box's is tested in the
     // warp-uniform list instead of living in the tree (at most RTB_MAX_LARGE, the largest first)
-    std::vector<int> large, small;
+    std::vector<int> large, small, small_idx;  // small_idx: position of each tree primitive in f.leaf_refs / f.leaf_box
     if (c->opt_large_split && !f.leaf_refs.empty()) {
         float e[3] = {f.hi[0] - f.lo[0], f.hi[1] - f.lo[1], f.hi[2] - f.lo[2]};
         float scene_area = 2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
@@ -1034,9 +1180,13 @@ static int scene_commit_timed(rtb_ctx *c) {
         if ((int)cand.size() > std::min(c->opt_max_large, 32)) cand.resize(std::max(0, std::min(c->opt_max_large, 32)));  // bit masks of 32
         std::vector<char> is_large(f.leaf_refs.size(), 0);
         for (auto &pr : cand) is_large[pr.second] = 1;
-        for (size_t i = 0; i < f.leaf_refs.size(); i++) (is_large[i] ? large : small).push_back(f.leaf_refs[i]);
+        for (size_t i = 0; i < f.leaf_refs.size(); i++) {
+            (is_large[i] ? large : small).push_back(f.leaf_refs[i]);
+            if (!is_large[i]) small_idx.push_back((int)i);
+        }
     } else {
         small = f.leaf_refs;
+        for (size_t i = 0; i < f.leaf_refs.size(); i++) small_idx.push_back((int)i);
     }
     const int *d_small = nullptr;
     // padded boxes of the large primitives (conservative pre-test before the exact one)
@@ -1052,7 +1202,32 @@ static int scene_commit_timed(rtb_ctx *c) {
                 float pad = 4e-7f * fmaxf(fmaxf(fabsf(b[k]), fabsf(b[3 + k])), b[3 + k] - b[k]) + 1e-12f;
                 lo[k] = b[k] - pad; hi[k] = b[3 + k] + pad;
             }
-            large_boxes.push_back(make_float4(lo[0], lo[1], lo[2], 0.f));
+            // A primitive that is flat on a coordinate axis (walls, floors: every side vector has an exactly zero
+            // component there) gets that axis + 1 in lo.w: large_prims_best then proves, from the slab of that axis
+            // alone, that Triangle::hit would return a distance below its 1e-6 threshold (the ray STARTS on this
+            // wall) and skips the two exact tests.  See the derivation there.
+            int flat_axis = 0;
+            {
+                int enc = ~large[li], kind = enc & 7, idx = enc >> RTB_KIND_BITS;
+                if (kind != KIND_SPHERE) {
+                    int count = kind == KIND_TRI ? 1 : 2;
+                    bool flat[3] = {true, true, true};
+                    for (int t = 0; t < count; t++) {
+                        float4 ta = f.tris[3 * (size_t)(idx + t)], tb = f.tris[3 * (size_t)(idx + t) + 1], tc = f.tris[3 * (size_t)(idx + t) + 2];
+                        float s1[3] = {ta.w, tb.x, tb.y}, s2[3] = {tb.z, tb.w, tc.x};
+                        for (int k2 = 0; k2 < 3; k2++) flat[k2] = flat[k2] && s1[k2] == 0.f && s2[k2] == 0.f;
+                        if (t == 1) {  // both triangles of a quad start at the same point (Quad::create_triangles, objects.cu:244-253)
+                            float4 t0 = f.tris[3 * (size_t)idx];
+                            if (t0.x != ta.x || t0.y != ta.y || t0.z != ta.z) flat[0] = flat[1] = flat[2] = false;
+                        }
+                    }
+                    for (int k2 = 0; k2 < 3; k2++)
+                        if (flat[k2] && flat_axis == 0) flat_axis = k2 + 1;
+                }
+            }
+            float4 lo4 = make_float4(lo[0], lo[1], lo[2], 0.f);
+            std::memcpy(&lo4.w, &flat_axis, sizeof(int));
+            large_boxes.push_back(lo4);
             large_boxes.push_back(make_float4(hi[0], hi[1], hi[2], 0.f));
             li++;
         }
@@ -1076,9 +1251,21 @@ static int scene_commit_timed(rtb_ctx *c) {
     in.leaf_refs = d_small;
     in.tris = d.tris; in.spheres = d.spheres;
     float4 *nodes = nullptr;
-    int root = 0;
+    int root = 0, height = 0;
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "timing LBVH build");
-    RTB_CUDA(c, lbvh_build(in, &nodes, &root, c->stream, c->opt_builder, c->opt_ploc_radius), "building LBVH");
+    if (c->opt_builder == 2 && in.num_prims >= 2) {
+        // EXPERIMENT: full-sweep SAH on the host (tree-quality yardstick for the GPU builders)
+        std::vector<float4> hn;
+        height = sah_build_host(f.leaf_box, small_idx, small, hn);
+        RTB_CUDA(c, cudaMalloc((void **)&nodes, hn.size() * sizeof(float4)), "allocating SAH nodes");
+        RTB_CUDA(c, cudaMemcpyAsync(nodes, hn.data(), hn.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream), "uploading SAH nodes");
+        root = 0;
+    } else {
+        cudaError_t be = lbvh_build(in, &nodes, &root, &height, c->stream, c->opt_builder == 2 ? 1 : c->opt_builder, c->opt_ploc_radius);
+        if (be == cudaErrorNotSupported)  // a PLOC round merged nothing: the Karras hierarchy always exists
+            be = lbvh_build(in, &nodes, &root, &height, c->stream, 0, c->opt_ploc_radius);
+        RTB_CUDA(c, be, "building LBVH");
+    }
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "timing LBVH build");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "building LBVH");
     float ms = 0;
@@ -1087,6 +1274,27 @@ static int scene_commit_timed(rtb_ctx *c) {
     if (nodes) {
         c->scene_allocs.push_back(nodes);
         c->scene_bytes += sizeof(float4) * 4 * (size_t)(d.num_bvh_prims - 1);
+    }
+    c->tree_height = height;
+    // the traversal keeps one stack entry per level (rtb_trace.cuh): a deeper tree would drop far children
+    if (height > RTB_STACK - 2 && c->opt_builder != 0) {  // PLOC has no depth bound (nested / sorted input): try the Karras hierarchy
+        float4 *nodes2 = nullptr;
+        int root2 = 0, height2 = 0;
+        RTB_CUDA(c, lbvh_build(in, &nodes2, &root2, &height2, c->stream, 0, c->opt_ploc_radius), "building LBVH");
+        if (nodes2 && height2 < height) {
+            c->scene_allocs.back() = nodes2;
+            cudaFree(nodes);
+            nodes = nodes2; root = root2; height = height2;
+            c->tree_height = height;
+        } else if (nodes2) {
+            cudaFree(nodes2);
+        }
+    }
+    if (height > RTB_STACK - 2) {
+        char msg[160];
+        std::snprintf(msg, sizeof msg, "the tree over this scene is %d levels high; the traversal stack holds %d (duplicate or nested primitives?)", height, RTB_STACK - 2);
+        free_scene(c);
+        return fail(c, "building LBVH", msg);
     }
     d.nodes = nodes;
     d.root_ref = root;
@@ -1147,25 +1355,46 @@ int rtb_render(rtb_ctx *c, float *rgb_inout, int *frame_num_inout, int current_t
     size_t bytes = c->image_floats * sizeof(float);
     RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_inout, bytes, cudaMemcpyHostToDevice, c->stream), "copying previous render");
     if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream), "clearing counters");
+    if (rtb_exchange_after_local_write(c) != 0) return 1;
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
-    if (launch_frame(c, current_time_ms, *frame_num_inout) != 0) return 1;
+    if (launch_frame(c, frame_time(c, current_time_ms, 0, 1), *frame_num_inout) != 0) return 1;
+    if (rtb_exchange_frame(c) != 0) return 1;
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "render");
     RTB_CUDA(c, cudaMemcpyAsync(rgb_inout, c->d_image, bytes, cudaMemcpyDeviceToHost, c->stream), "copying image to host");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "final check after render");
+    if (check_stream_watchdog(c) != 0) return 1;
     c->timing_pending = true;
     (*frame_num_inout)++;
     c->frame_num = *frame_num_inout;
     return fetch_counters(c);
 }
 
-int rtb_render_device(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) {
+static int render_frames(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms, bool exchange) {
     if (!c || n_frames < 0) return 1;
     Bind b(c);
     if (check_ready(c) != 0) return 1;
     if (c->opt_counters) RTB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream), "clearing counters");
     RTB_CUDA(c, cudaEventRecord(c->ev0, c->stream), "render");
     for (int k = 0; k < n_frames; k++) {
-        if (launch_frame(c, time0_ms + k * time_step_ms, c->frame_num) != 0) return 1;
+        // Bounded run-ahead: at most two frames are enqueued beyond the one the device works on.  A wavefront frame is
+        // hundreds to thousands of launches on two streams; with tens of frames queued ahead the device showed a gap
+        // of ~25 ms between 148 ms frames (C4 at 4K, measured), with two it shows none.
+        if (c->opt_run_ahead > 0) {
+            if (c->frames_enqueued >= c->opt_run_ahead) {
+                cudaEvent_t &old = c->frame_done[(c->frames_enqueued - c->opt_run_ahead) % 4];
+                if (old) RTB_CUDA(c, cudaEventSynchronize(old), "waiting for an earlier frame");
+            }
+        }
+        if (launch_frame(c, frame_time(c, time0_ms, k, time_step_ms), c->frame_num) != 0) return 1;
+        {
+            cudaEvent_t &done = c->frame_done[c->frames_enqueued % 4];
+            if (!done) RTB_CUDA(c, cudaEventCreateWithFlags(&done, cudaEventDisableTiming), "creating frame events");
+            RTB_CUDA(c, cudaEventRecord(done, c->stream), "marking the end of a frame");
+            c->frames_enqueued++;
+        }
+        // tiles: the image is complete on every rank after each frame (the next frame's running mean reads it);
+        // sample slices: the mean over all ranks' frames so far
+        if (exchange && rtb_exchange_frame(c) != 0) return 1;
         c->frame_num++;
     }
     RTB_CUDA(c, cudaEventRecord(c->ev1, c->stream), "render");
@@ -1173,10 +1402,13 @@ int rtb_render_device(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) 
     return 0;
 }
 
+int rtb_render_device(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) { return render_frames(c, n_frames, time0_ms, time_step_ms, true); }
+
 int rtb_sync(rtb_ctx *c) {
     if (!c) return 1;
     Bind b(c);
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "final check after render");
+    if (check_stream_watchdog(c) != 0) return 1;
     return fetch_counters(c);
 }
 
@@ -1186,7 +1418,7 @@ int rtb_reset_accumulation(rtb_ctx *c) {
     if (ensure_image(c) != 0) return 1;
     RTB_CUDA(c, cudaMemsetAsync(c->d_image, 0, c->image_floats * sizeof(float), c->stream), "clearing image");
     c->frame_num = 0;
-    return 0;
+    return rtb_exchange_after_local_write(c);
 }
 
 int rtb_set_accumulation(rtb_ctx *c, const float *rgb_host, int frame_num) {
@@ -1194,8 +1426,9 @@ int rtb_set_accumulation(rtb_ctx *c, const float *rgb_host, int frame_num) {
     Bind b(c);
     if (ensure_image(c) != 0) return 1;
     RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_host, c->image_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream), "copying previous render");
-    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying previous render");
     c->frame_num = frame_num;
+    if (rtb_exchange_after_local_write(c) != 0) return 1;
+    RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying previous render");
     return 0;
 }
 
@@ -1205,6 +1438,7 @@ int rtb_download(rtb_ctx *c, float *rgb_host, int *frame_num_out) {
     if (ensure_image(c) != 0) return 1;
     RTB_CUDA(c, cudaMemcpyAsync(rgb_host, c->d_image, c->image_floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream), "copying image to host");
     RTB_CUDA(c, cudaStreamSynchronize(c->stream), "copying image to host");
+    if (check_stream_watchdog(c) != 0) return 1;
     if (frame_num_out) *frame_num_out = c->frame_num;
     return 0;
 }
@@ -1341,8 +1575,16 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     c->auto_choice = -1;  // every option shapes the kernels: tune again at the next frame
     if (k == "counters") c->opt_counters = value;
     else if (k == "traversal") c->opt_traversal = value;
-    else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; c->pool_per_sm = 0; }
-    else if (k == "tune_set") c->opt_tune_set = value & 11;   // kernels the timed choice tries: 1 megakernel, 2 wavefront, 8 pooled
+    else if (k == "strict_fp") { c->opt_strict = value; c->wf_shade_per_sm = 0; c->pool_per_sm = 0; c->stream_per_sm = 0; }
+    else if (k == "exchange") {
+        if (value < 0 || value > 2) return fail(c, "rtb_set_option", "exchange: 0 = caller's, 1 = NCCL all-gather / all-reduce, 2 = fused peer stores");
+        c->opt_exchange = value;
+    }
+    else if (k == "slices") c->opt_slices = value != 0;
+    else if (k == "run_ahead") c->opt_run_ahead = value < 0 ? 0 : (value > 3 ? 3 : value);   // frames enqueued ahead of the device (0 = unbounded)
+    else if (k == "tune_set") c->opt_tune_set = value & 27;   // kernels the timed choice tries: 1 megakernel, 2 wavefront, 8 pooled, 16 streaming
+    else if (k == "stream_slots") c->opt_stream_slots = value < 1 ? 1 : value;
+    else if (k == "stream_shade_sms") { c->opt_stream_shade_sms = value; c->stream_shade_sms = 0; }
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
     else if (k == "builder") c->opt_builder = value;
     else if (k == "ploc_radius") c->opt_ploc_radius = value;
@@ -1356,7 +1598,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "wf_streams") c->opt_wf_streams = value < 1 ? 1 : value;
     else if (k == "wf_refill") c->opt_wf_refill = value;  // free lanes before a traversal warp fetches new rays
     else if (k == "kernel") {
-        if (value < 0 || value > 3) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice), 3 = pooled persistent kernel");
+        if (value < 0 || value > 4) return fail(c, "rtb_set_option", "kernel: 0 = megakernel, 1 = wavefront, 2 = auto (timed choice), 3 = pooled persistent kernel, 4 = streaming kernel");
         c->opt_kernel = value;
     }
     else if (k == "block_threads") {
@@ -1401,6 +1643,10 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "num_spheres") *value = c->d.num_spheres;
     else if (k == "num_nodes") *value = c->d.num_bvh_prims > 1 ? c->d.num_bvh_prims - 1 : 0;
     else if (k == "num_large") *value = c->d.num_large;
+    else if (k == "tree_height") *value = c->tree_height;
+    else if (k == "exchange") *value = c->opt_exchange;
+    else if (k == "exchange_fused") *value = (c->opt_exchange == 2 && !c->opt_slices && c->n_peers == c->shard_world && c->shard_world > 1) ? 1 : 0;
+    else if (k == "comm_world") *value = c->comm ? c->comm_world : 1;
     else if (k == "build_ms") *value = c->build_ms;
     else if (k == "commit_ms") *value = c->commit_ms;
     else if (k == "kernel") *value = effective_kernel(c);      // the variant frames are rendered with
@@ -1409,6 +1655,11 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "tune_megakernel_ms") *value = c->tune_ms[0];
     else if (k == "tune_wavefront_ms") *value = c->tune_ms[1];
     else if (k == "tune_pool_ms") *value = c->tune_ms[3];
+    else if (k == "tune_stream_ms") *value = c->tune_ms[4];
+    else if (k == "stream_shade_sms") *value = c->stream_shade_sms;
+    else if (k == "stream_util_shade") *value = c->stream_util[0];
+    else if (k == "stream_util_traverse") *value = c->stream_util[1];
+    else if (k == "stream_slots") *value = (double)c->stream_slots;
     else if (k == "walk_min") *value = c->opt_walk_min > 0 ? c->opt_walk_min : (effective_kernel(c) != 0 ? c->tuned_walk_min : 8);
     else if (k == "wf_refill") *value = c->opt_wf_refill > 0 ? c->opt_wf_refill : c->tuned_refill;
     else if (k == "wf_shade_ms") *value = c->wf_shade_ms;
@@ -1436,3 +1687,14 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
 }
 
 }  // extern "C"
+
+// ---- internals used by rtb_comm.cu ---------------------------------------------------------------------------------
+int rtb_set_accumulation_async(rtb_ctx *c, const float *rgb_host, int frame_num) {
+    Bind b(c);
+    if (ensure_image(c) != 0) return 1;
+    RTB_CUDA(c, cudaMemcpyAsync(c->d_image, rgb_host, c->image_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream), "copying previous render");
+    c->frame_num = frame_num;
+    return 0;
+}
+
+int rtb_render_frames_no_exchange(rtb_ctx *c, int n_frames, int time0_ms, int time_step_ms) { return render_frames(c, n_frames, time0_ms, time_step_ms, false); }

@@ -12,6 +12,20 @@
 
 namespace rtb {
 
+// per-lane traversal stack entries (local memory); rtb_scene_commit refuses trees that would need more
+#ifndef RTB_STACK
+#define RTB_STACK 96
+#endif
+
+// -DRTB_CHECKS: device-side asserts on every queue / slot / stack index (the stand-in for compute-sanitizer,
+// which is closed on this GPU pool); a failed assert traps the kernel and the call returns an error
+#ifdef RTB_CHECKS
+#include <cassert>
+#define RTB_ASSERT(x) assert(x)
+#else
+#define RTB_ASSERT(x)
+#endif
+
 #define RTB_INF_F 1073741824.0f /* INF = 1 << 31 - 1 == 1 << 30, objects.cu:6 */
 #define RTB_EPS 0.000001f      /* FLOAT_PRECISION_ERROR, objects.cu:7 */
 
@@ -74,6 +88,16 @@ struct DScene {
     int num_tris, num_spheres, num_objects;
 };
 
+// Screen-tile sharding with the exchange fused into the render kernels: a finished pixel is stored into the
+// accumulation image of EVERY GPU of the job (peer memory over NVLink / NVSwitch: plain global stores through
+// cudaDeviceEnablePeerAccess or CUDA IPC mappings), so the frame needs no gather afterwards -- the transfer rides
+// along with the rendering, 12 bytes per peer per finished pixel.  n == 0: single GPU, store to `out` only.
+#define RTB_MAX_PEERS 8
+struct PeerOut {
+    float *image[RTB_MAX_PEERS];  // every rank's accumulation image, this rank's own included
+    int n;
+};
+
 struct DCamera {  // == DeviceCamData, camera.cu:12-18
     float cam_pos[3], tl[3], du[3], dv[3];
 };
@@ -120,7 +144,7 @@ __device__ __forceinline__ uint32_t rng_seed(int array_index, int time_ms) {
 //   fma(x, 2^-32, x) = RN(x + x * 2^-32), and the neglected tail (< 2^-64 relative) never moves
 //   the double rounding because x + x*2^-32 has at most 64 significant bits whose low part is far
 //   from a double rounding boundary -- verified exhaustively for all 2^32 inputs by
-//   tests/test_rng_exhaustive.py (CPU) before being enabled.
+//   tests/rng_exhaustive.c (run by tests/test_cpu_oracle.py) before being enabled.
 __device__ __forceinline__ float rng_to_float(uint32_t r) {
 #ifdef RTB_RNG_FMA
     double x = (double)r * 2.3283064365386963e-10;  // 2^-32, exact

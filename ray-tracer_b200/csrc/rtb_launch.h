@@ -13,6 +13,7 @@ struct RenderParams {
     int time_ms, frame_num;
     const float *prev;  // previous running mean (may alias out)
     float *out;
+    PeerOut peers;      // fused tile exchange: every rank's image (n == 0: none)
     // screen-tile sharding: this launch renders rows y with (y / band_rows) % world == rank
     int shard_rank, shard_world, band_rows;
     int local_rows;                  // rows owned by this rank
@@ -43,6 +44,7 @@ struct WfParams {
     int time_ms, frame_num;
     const float *prev;
     float *out;
+    PeerOut peers;
     int shard_rank, shard_world, band_rows, local_rows;
     int slot_base, slot_count;  // the row group this launch works on: slots [slot_base, slot_base + slot_count)
     WfState st;
@@ -68,10 +70,45 @@ struct PoolParams {
     int time_ms, frame_num;
     const float *prev;
     float *out;
+    PeerOut peers;
     int shard_rank, shard_world, band_rows, local_rows;
     int refill, walk_min;
     float4 *pool;                 // 6 planes of 64 float4 per warp of the grid
     unsigned int *work_counter;   // zeroed before launch
+    unsigned long long *counters;
+};
+
+// ---- streaming kernel (rtb_stream.cuh) -------------------------------------------------------------
+#ifndef RTB_STREAM_SHARDS
+#define RTB_STREAM_SHARDS 8   // sub-queues per queue (a power of two)
+#endif
+struct StreamQueue {
+    int *ring;            // RTB_STREAM_SHARDS rings of (mask + 1) entries: 0 = empty, else (slot + 1) | lap << 31
+    unsigned int *head;   // per shard, 32 words apart
+    unsigned int *tail;
+    unsigned int mask;
+};
+
+struct StreamParams {
+    DScene scene;
+    DCamera cam;
+    DRender rd;
+    int width, height;
+    int time_ms, frame_num;
+    const float *prev;
+    float *out;
+    PeerOut peers;
+    int shard_rank, shard_world, band_rows, local_rows;
+    int refill, walk_min;
+    WfState st;                  // six planes of num_slots float4
+    unsigned int *pix;           // per slot: x | y << 16
+    StreamQueue rq, hq;          // rays to traverse / hits to shade
+    unsigned int *ctl;           // control words (rtb_stream.cuh), zeroed before launch
+    int *sm_role;                // per %smid: 0 = not drawn yet, 1 = SHADE, 2 = TRAVERSE; zeroed before launch
+    unsigned long long *stats;   // [0] shade busy lane-cycles, [1] shade lane-cycles, [2] traverse busy, [3] traverse total
+    int num_slots;
+    unsigned int total_pixels;
+    int shade_sms, total_sms;
     unsigned long long *counters;
 };
 
@@ -91,6 +128,9 @@ struct LaunchConfig {
     cudaError_t launch_pool(const PoolParams &p, bool brute, bool count, int blocks, cudaStream_t st);              \
     cudaError_t pool_occupancy(int *blocks_per_sm);                                                                 \
     int pool_block_threads();                                                                                       \
+    cudaError_t launch_stream(const StreamParams &p, bool brute, bool count, int blocks, cudaStream_t st);          \
+    cudaError_t stream_occupancy(int *blocks_per_sm);                                                               \
+    int stream_block_threads();                                                                                     \
     }
 RTB_DECLARE_VARIANT(fast)
 RTB_DECLARE_VARIANT(strict)

@@ -49,9 +49,19 @@ __global__ void leaf_bounds_kernel(LbvhInput in, float4 *leaf_lo, float4 *leaf_h
     } else {
         float4 s = in.spheres[idx];
         float r = fabsf(s.w) * 1.000001f;
+        if (!(r <= 1.0e18f)) r = 1.0e18f;  // NaN or overflowing radius
         grow(lo, hi, s.x - r, s.y - r, s.z - r);
         grow(lo, hi, s.x + r, s.y + r, s.z + r);
     }
+    // A NaN / inf vertex (or a radius that overflows) must not poison the tree: fminf / fmaxf dropped the NaNs, the
+    // clamp keeps every extent and every union area finite (1e18^2 < FLT_MAX).  The reference renders such a scene
+    // (the primitive simply never hits); so does this tree, with the primitive in a huge box.
+    const float BIG = 1.0e18f;
+    lo.x = fminf(fmaxf(lo.x, -BIG), BIG); lo.y = fminf(fmaxf(lo.y, -BIG), BIG); lo.z = fminf(fmaxf(lo.z, -BIG), BIG);
+    hi.x = fminf(fmaxf(hi.x, -BIG), BIG); hi.y = fminf(fmaxf(hi.y, -BIG), BIG); hi.z = fminf(fmaxf(hi.z, -BIG), BIG);
+    if (!(lo.x <= hi.x)) { lo.x = -BIG; hi.x = BIG; }   // no finite vertex on this axis at all
+    if (!(lo.y <= hi.y)) { lo.y = -BIG; hi.y = BIG; }
+    if (!(lo.z <= hi.z)) { lo.z = -BIG; hi.z = BIG; }
     leaf_lo[i] = make_float4(lo.x, lo.y, lo.z, 0.f);
     leaf_hi[i] = make_float4(hi.x, hi.y, hi.z, 0.f);
     float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
@@ -226,8 +236,10 @@ __global__ void refit_kernel(int n, const int *vals, const float4 *leaf_lo, cons
         float4 l0, h0, l1, h1;
         if (c.x >= 0) { l0 = __ldcg(node_lo + c.x); h0 = __ldcg(node_hi + c.x); } else { l0 = leaf_lo[vals[~c.x]]; h0 = leaf_hi[vals[~c.x]]; }
         if (c.y >= 0) { l1 = __ldcg(node_lo + c.y); h1 = __ldcg(node_hi + c.y); } else { l1 = leaf_lo[vals[~c.y]]; h1 = leaf_hi[vals[~c.y]]; }
+        // hi.w carries the height of the subtree (a leaf counts 0): the traversal stack needs one entry per level
+        float hl = c.x >= 0 ? h0.w : 0.f, hr = c.y >= 0 ? h1.w : 0.f;
         __stcg(node_lo + node, make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f));
-        __stcg(node_hi + node, make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.f));
+        __stcg(node_hi + node, make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), fmaxf(hl, hr) + 1.f));
         node = parent_internal[node];
     }
 }
@@ -281,6 +293,7 @@ __global__ void ploc_init_kernel(int n, const int *vals, const int *leaf_refs, c
     int v = vals[i];
     float4 lo = leaf_lo[v], hi = leaf_hi[v];
     lo.w = __int_as_float(leaf_refs[v]);
+    hi.w = 0.f;  // height of the cluster's subtree
     clo[i] = lo;
     chi[i] = hi;
 }
@@ -326,7 +339,7 @@ __global__ void ploc_merge_kernel(int n, const int *nn, float4 *clo, float4 *chi
     padded(blo, bhi, __float_as_int(blo.w), olo, ohi);
     nodes[4 * node + 2] = olo; nodes[4 * node + 3] = ohi;
     clo[i] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(node));
-    chi[i] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+    chi[i] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), fmaxf(ahi.w, bhi.w) + 1.f);
     keep[i] = 1;
 }
 
@@ -386,9 +399,10 @@ __global__ void init_bounds_kernel(unsigned int *b) {
 
 #define LBVH_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
-cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, cudaStream_t st, int builder, int ploc_radius) {
+cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, int *height_out, cudaStream_t st, int builder, int ploc_radius) {
     *nodes_out = nullptr;
     *root_ref = 0;
+    *height_out = 0;
     const int n = in.num_prims;
     if (n <= 0) return cudaSuccess;
     if (n == 1) {
@@ -459,22 +473,30 @@ cudaError_t lbvh_build(const LbvhInput &in, float4 **nodes_out, int *root_ref, c
             int next = 0;
             LBVH_CHECK(cudaMemcpyAsync(&next, total, sizeof(int), cudaMemcpyDeviceToHost, st));
             LBVH_CHECK(cudaStreamSynchronize(st));
-            if (next <= 0 || next >= count) { err = cudaErrorUnknown; goto done; }  // cannot happen: the cheapest pair is mutual
+            // cannot happen with finite boxes (the cheapest pair is mutual), and leaf_bounds_kernel makes them finite;
+            // should it happen anyway, say so instead of hanging: the caller falls back to the Karras builder
+            if (next <= 0 || next >= count) { err = cudaErrorNotSupported; goto done; }
             count = next;
             float4 *t0 = clo; clo = clo_alt; clo_alt = t0;
             t0 = chi; chi = chi_alt; chi_alt = t0;
         }
-        float4 root;
+        float4 root, root_hi;
         LBVH_CHECK(cudaMemcpyAsync(&root, clo, sizeof(float4), cudaMemcpyDeviceToHost, st));
+        LBVH_CHECK(cudaMemcpyAsync(&root_hi, chi, sizeof(float4), cudaMemcpyDeviceToHost, st));
         LBVH_CHECK(cudaStreamSynchronize(st));
         int root_node;
         std::memcpy(&root_node, &root.w, sizeof(int));
         *root_ref = root_node;
+        *height_out = (int)root_hi.w;
     } else {
         karras_kernel<<<B, T, 0, st>>>(n, keys, children, parent_internal, parent_leaf);
         refit_kernel<<<B, T, 0, st>>>(n, vals, leaf_lo, leaf_hi, children, parent_internal, parent_leaf, node_lo, node_hi, flags);
         pack_nodes_kernel<<<B, T, 0, st>>>(n, vals, in.leaf_refs, leaf_lo, leaf_hi, children, node_lo, node_hi, nodes);
         *root_ref = 0;
+        float4 root_hi;
+        LBVH_CHECK(cudaMemcpyAsync(&root_hi, node_hi, sizeof(float4), cudaMemcpyDeviceToHost, st));
+        LBVH_CHECK(cudaStreamSynchronize(st));
+        *height_out = (int)root_hi.w;
     }
     LBVH_CHECK(cudaGetLastError());
     LBVH_CHECK(cudaStreamSynchronize(st));

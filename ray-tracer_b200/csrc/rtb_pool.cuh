@@ -118,6 +118,8 @@ __global__ void __launch_bounds__(RTB_POOL_THREADS, RTB_POOL_MIN_BLOCKS) pool_re
                 bool fresh = live && (int)lane >= n_ready;
                 if (fresh) slot = take[lane - n_ready];
                 unsigned long long batch = from_ready | from_empty;
+                RTB_ASSERT(!live || (slot >= 0 && slot < RTB_POOL_SLOTS && ((batch >> slot) & 1ull)));
+                RTB_ASSERT(__popcll(batch) == n_batch && !(from_ready & from_empty) && !(batch & trav_ready));
                 int array_index = -1;
                 V3 pdir = v3(0, 0, 1);
                 Path P;
@@ -159,13 +161,14 @@ __global__ void __launch_bounds__(RTB_POOL_THREADS, RTB_POOL_MIN_BLOCKS) pool_re
                             int y = shard_row(p.shard_rank, p.shard_world, p.band_rows, ly);
                             if (y >= p.height) continue;
                             array_index = (y * p.width + x) * 3;  // raytracer.cu:123
+                            RTB_ASSERT(array_index >= 0 && array_index + 2 < p.width * p.height * 3);
                             pix[slot] = (unsigned int)x | ((unsigned int)y << 16);
                             path_begin_pixel(P, array_index, p.time_ms);
                             pdir = primary_direction(p.cam, x, y);
                         }
                         if (P.bounce == 0) {
                             if (P.sample >= f.spp) {
-                                path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
+                                path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, p.peers, array_index);
                                 array_index = -1;
                                 continue;
                             }
@@ -215,6 +218,7 @@ __global__ void __launch_bounds__(RTB_POOL_THREADS, RTB_POOL_MIN_BLOCKS) pool_re
                 int rank = __popc(want & ((1u << lane) - 1u));
                 if (tslot < 0 && rank < n_take) {
                     tslot = take[rank];
+                    RTB_ASSERT(tslot >= 0 && tslot < RTB_POOL_SLOTS && ((taken >> tslot) & 1ull));
                     float4 o = pool_ld(stO + tslot), d = pool_ld(stD + tslot), h = pool_ld(stH + tslot);
                     ray.o = v3(o.x, o.y, o.z);
                     ray.d = v3(d.x, d.y, d.z);

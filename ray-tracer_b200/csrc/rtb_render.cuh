@@ -236,14 +236,24 @@ __device__ __forceinline__ void path_begin_pixel(Path &P, int array_index, int t
 }
 
 // get_ray_colour's tail, raytracer.cu:107-112: mean over the samples, then the progressive mean
-__device__ __forceinline__ void path_write_pixel(const Path &P, int spp, int frame_num, const float *prev, float *out, int array_index) {
+__device__ __forceinline__ void path_write_pixel(const Path &P, int spp, int frame_num, const float *prev, float *out, const PeerOut &peers, int array_index) {
     V3 colour = P.acc / (float)spp;
     V3 previous = v3(prev[array_index], prev[array_index + 1], prev[array_index + 2]);
     V3 previous_sum = previous * (float)frame_num;
     V3 res = (colour + previous_sum) / (float)(frame_num + 1);
-    out[array_index] = res.x;
-    out[array_index + 1] = res.y;
-    out[array_index + 2] = res.z;
+    if (peers.n == 0) {
+        out[array_index] = res.x;
+        out[array_index + 1] = res.y;
+        out[array_index + 2] = res.z;
+        return;
+    }
+    // fused exchange of the tile sharding: the pixel goes to every GPU's image (this GPU's own is one of them)
+    for (int r = 0; r < peers.n; r++) {
+        float *img = peers.image[r];
+        img[array_index] = res.x;
+        img[array_index + 1] = res.y;
+        img[array_index + 2] = res.z;
+    }
 }
 
 // trace_ray(ray) starts from a copy of the primary ray, raytracer.cu:67-69,103
@@ -325,12 +335,13 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
                         int y = shard_row(p.shard_rank, p.shard_world, p.band_rows, ly);
                         if (y >= p.height) continue;
                         array_index = (y * p.width + x) * 3;  // raytracer.cu:123
+                        RTB_ASSERT(array_index >= 0 && array_index + 2 < p.width * p.height * 3);
                         path_begin_pixel(P, array_index, p.time_ms);
                         pdir = primary_direction(p.cam, x, y);
                     }
                     if (P.bounce == 0) {
                         if (P.sample >= f.spp) {
-                            path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
+                            path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, p.peers, array_index);
                             array_index = -1;
                             continue;
                         }
@@ -438,6 +449,7 @@ cudaError_t render_occupancy(int threads, int *blocks_per_sm) {
 
 #include "rtb_wavefront.cuh"
 #include "rtb_pool.cuh"
+#include "rtb_stream.cuh"
 
 }  // namespace RTB_NS
 }  // namespace rtb

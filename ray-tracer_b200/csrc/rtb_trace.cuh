@@ -110,6 +110,7 @@ __device__ __forceinline__ void consider(const DScene &s, Best &best, float t, f
 // quads (two consecutive triangles) so that lanes holding either kind stay converged.
 __device__ __forceinline__ void test_leaf(const DScene &s, const Ray &r, int ref, Best &best, Counters &cnt) {
     int enc = ~ref, kind = enc & 7, idx = enc >> RTB_KIND_BITS;
+    RTB_ASSERT(ref < 0 && idx >= 0 && (kind == KIND_SPHERE ? idx < s.num_spheres : idx + (kind == KIND_TRI ? 0 : 1) < s.num_tris));
     float t, u = 0, v = 0;
     if (kind == KIND_SPHERE) {
         RTB_COUNT(cnt, sph);
@@ -157,10 +158,6 @@ __device__ __forceinline__ bool box_test(float4 lo, float4 hi, const Ray &r, flo
     return tmin <= tmax * 1.000004f;
 }
 
-#ifndef RTB_STACK
-#define RTB_STACK 96
-#endif
-
 #define RTB_DONE 0x7fffffff
 
 // Resumable traversal state of one ray: lives in the lane across iterations of the megakernel's
@@ -190,7 +187,24 @@ __device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, 
     for (int i = 0; i < s.num_large; i++) {
         float tn;
         RTB_COUNT(cnt, box);
-        if (box_test(s.large_box_c[2 * i], s.large_box_c[2 * i + 1], r, RTB_INF_F, tn)) cand |= 1u << i;
+        const float4 lo = s.large_box_c[2 * i], hi = s.large_box_c[2 * i + 1];
+        bool c = box_test(lo, hi, r, RTB_INF_F, tn);
+        // A ray that STARTS on a wall meets that wall's box at t ~ 0, and Triangle::hit (objects.cu:135-163) then
+        // runs twice only to fail `dist > 1e-6`.  For a primitive that is flat on axis k (every side vector has an
+        // exactly zero k component, checked at commit) the products of Triangle::hit that multiply those zeros vanish
+        // exactly, and what remains is dist = -(o_k - p0_k) / d_k up to the rounding of a 2-D cross product that is
+        // formed the same way in numerator and denominator (relative error a few 1e-7 / sin(angle between the sides)).
+        // o_k - p0_k is exact (Sterbenz) and lies inside the padded slab, so max((lo_k - o_k) / d_k, (hi_k - o_k) / d_k)
+        // bounds dist from above: below 0.99e-6 the reference's test rejects both triangles, whatever u and v say.
+        // NaN / inf (d_k == 0) compare false and take the exact tests.
+        int flat_axis = __float_as_int(lo.w);
+        if (flat_axis) {
+            float lk = flat_axis == 1 ? lo.x : (flat_axis == 2 ? lo.y : lo.z), hk = flat_axis == 1 ? hi.x : (flat_axis == 2 ? hi.y : hi.z);
+            float ok = flat_axis == 1 ? r.o.x : (flat_axis == 2 ? r.o.y : r.o.z), ik = flat_axis == 1 ? r.inv.x : (flat_axis == 2 ? r.inv.y : r.inv.z);
+            float tk = fmaxf((lk - ok) * ik, (hk - ok) * ik);
+            if (tk < 0.99e-6f) c = false;
+        }
+        if (c) cand |= 1u << i;
     }
     // Triangles and quads: one Triangle::hit per lane and step, whatever the lane's candidate is (a
     // single triangle, or triangle 1 / triangle 2 of a quad), so lanes with different candidate lists
@@ -320,15 +334,17 @@ __device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &
 // quota: leave once this many lanes of the WARP hold a finished (or no) ray; <= 0 = run to completion.
 // NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
 // traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
+// max_rounds > 0: come back after that many rounds whatever the lanes did (a caller that polls a queue).
 template <int NODE_STEPS = 1>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
-                                         Counters &cnt) {
+                                         Counters &cnt, int max_rounds = 0) {
     (void)mask;
     int cur = T.cur, leaf = T.leaf, sp = T.sp, top = T.top;
     Best best = T.best;
     // every round retires at least one node step or one leaf of some lane; the cap only turns a
     // logic error into a wrong pixel (caught by the parity tests) instead of a hung GPU
-    for (int round = 0; round < (1 << 22); round++) {
+    const int round_cap = max_rounds > 0 ? max_rounds : (1 << 22);
+    for (int round = 0; round < round_cap; round++) {
         unsigned finished;
         for (;;) {
             bool walk = (unsigned)cur < (unsigned)RTB_DONE;  // an internal node index
@@ -343,6 +359,7 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
 #pragma unroll
             for (int step = 0; step < NODE_STEPS; step++) {
                 if ((unsigned)cur < (unsigned)RTB_DONE) {
+                    RTB_ASSERT(cur < s.num_bvh_prims - 1);
                     const float4 *N = s.nodes + 4 * cur;
                     float4 lo0, hi0, lo1, hi1;
                     load_node(N, lo0, hi0, lo1, hi1);
@@ -359,7 +376,9 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                     // four outcomes would otherwise run as four divergent paths
                     bool first0 = h0 && (!h1 || n0 <= n1);
                     int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
-                    if (h0 && h1 && sp < RTB_STACK) { T.stack[sp++] = top; top = far; }
+                    // the stack cannot overflow: rtb_scene_commit refuses a tree higher than RTB_STACK - 2
+                    RTB_ASSERT(!(h0 && h1) || sp < RTB_STACK);
+                    if (h0 && h1) { T.stack[sp++] = top; top = far; }
                     cur = near;
                     // a pop takes the register-held top; stack[0] holds RTB_DONE as a sentinel (sp >= 1), so
                     // the refill of `top` is an unconditional load

@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
         ray.o = f.cam_o; ray.d = v3(0, 0, 1); ray.inv = ray.d;
         if (live) {
             slot = p.first ? p.slot_base + (int)i : p.queue_in[i];
+            RTB_ASSERT(slot >= p.slot_base && slot < p.slot_base + p.slot_count);
             int x, y;
             wf_slot_to_pixel(p, slot, x, y);
             int array_index = (y * p.width + x) * 3;  // raytracer.cu:123
@@ -84,7 +85,7 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
             for (;;) {
                 if (P.bounce == 0) {
                     if (P.sample >= f.spp) {
-                        path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, array_index);
+                        path_write_pixel(P, f.spp, p.frame_num, p.prev, p.out, p.peers, array_index);
                         live = false;
                         p.alive[slot] = 0;
                         break;
@@ -127,11 +128,13 @@ __global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(con
         unsigned int tpos = 0;
         if (lane == 0 && entering) tpos = atomicAdd(p.tn, (unsigned int)__popc(entering));
         tpos = __shfl_sync(0xffffffffu, tpos, 0);
+        RTB_ASSERT(!enter || tpos + __popc(entering) <= (unsigned int)p.slot_count);
         if (enter) p.tqueue[tpos + __popc(entering & ((1u << lane) - 1u))] = slot;
         // compaction: the survivors of this warp go to consecutive queue positions, in order
         unsigned int pos = 0;
         if (lane == 0 && alive) pos = atomicAdd(p.n_out, (unsigned int)__popc(alive));
         pos = __shfl_sync(0xffffffffu, pos, 0);
+        RTB_ASSERT(!live || pos + __popc(alive) <= (unsigned int)p.slot_count);
         if (live) p.queue_out[pos + __popc(alive & ((1u << lane) - 1u))] = slot;
     }
     if (COUNT && p.counters) {
@@ -184,7 +187,9 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
             bool fresh = slot < 0 && mine < n;
             if (pos + __popc(want) >= n) exhausted = true;
             if (fresh) {
+                RTB_ASSERT(mine < (unsigned int)p.slot_count);
                 slot = p.tqueue[mine];
+                RTB_ASSERT(slot >= p.slot_base && slot < p.slot_base + p.slot_count);
                 float4 o = p.st.O[slot], d = p.st.D[slot], h = p.st.H[slot];
                 ray.o = v3(o.x, o.y, o.z);
                 ray.d = v3(d.x, d.y, d.z);

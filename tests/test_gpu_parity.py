@@ -115,7 +115,7 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
     tracer.setup(scene, W, H, 3, 6)
     out = []
     try:
-        for kernel in (0, 1, 3):
+        for kernel in (0, 1, 3, 4):
             tracer.set_option("kernel", kernel)
             tracer.set_option("counters", 1)
             img = np.zeros((H, W, 3), np.float32)
@@ -169,7 +169,7 @@ def test_wavefront_sharded_and_odd_sizes(tracer):
     tracer.set_option("kernel", 0)
     tracer.render(full, 0, 99)
     try:
-        for kernel in (1, 3):
+        for kernel in (1, 3, 4):
             tracer.set_option("kernel", kernel)
             combined = np.zeros((Hs, Ws, 3), np.float32)
             for rank in range(3):
@@ -183,12 +183,12 @@ def test_wavefront_sharded_and_odd_sizes(tracer):
         # strict-fp variant
         tracer.set_option("strict_fp", 1)
         imgs = []
-        for kernel in (1, 3, 0):
+        for kernel in (1, 3, 4, 0):
             tracer.set_option("kernel", kernel)
             a = np.zeros((Hs, Ws, 3), np.float32)
             tracer.render(a, 0, 5)
             imgs.append(a)
-        assert (imgs[0] == imgs[2]).all() and (imgs[1] == imgs[2]).all()
+        assert all((im == imgs[-1]).all() for im in imgs[:-1])
     finally:
         tracer.set_option("strict_fp", 0)
         tracer.set_option("kernel", 2)  # library default
@@ -354,12 +354,12 @@ def test_far_and_tiny_trees(tracer, scale, z):
                 tracer.set_scene(scene)
                 obj, sub, t = tracer.primary_ids()
                 imgs = []
-                for kernel in (0, 1, 3):
+                for kernel in (0, 1, 3, 4):
                     tracer.set_option("kernel", kernel)
                     img = np.zeros((H, W, 3), np.float32)
                     tracer.render(img, 0, 31)
                     imgs.append(img)
-                assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[2]).all()
+                assert all((im == imgs[0]).all() for im in imgs[1:])
                 results.append((obj, sub, t, imgs[0]))
             assert (results[0][0] >= 0).mean() > 0.2, "the mesh should cover a good part of the frame"
             for a, b in zip(results[0], results[1]):
@@ -388,8 +388,15 @@ def test_auto_kernel_choice(tracer):
             tracer.render(img, 1, 100)
             imgs[kernel] = img
         assert int(tracer.info("kernel_option")) == 2 and int(tracer.info("kernel_tuned")) == 1
-        assert int(tracer.info("kernel")) in (0, 1, 3)
-        assert tracer.info("tune_wavefront_ms") > 0 and tracer.info("tune_megakernel_ms") > 0 and tracer.info("tune_pool_ms") > 0
+        assert int(tracer.info("kernel")) in (0, 1)
+        assert tracer.info("tune_wavefront_ms") > 0 and tracer.info("tune_megakernel_ms") > 0
+        # the pooled and the streaming kernel join the timed choice on request
+        tracer.set_option("tune_set", 1 | 2 | 8 | 16)
+        img = np.zeros((H, W, 3), np.float32)
+        assert tracer.render(img, 0, 99) == 1
+        tracer.render(img, 1, 100)
+        assert tracer.info("tune_pool_ms") > 0 and tracer.info("tune_stream_ms") > 0 and (img == imgs[0]).all()
+        tracer.set_option("tune_set", 1 | 2)
         assert (imgs[0] == imgs[2]).all()
         # a new resolution tunes again
         tracer.setup(scene, 64, 48, 2, 3)
@@ -473,7 +480,7 @@ def test_edge_cases(tracer):
 
 
 def test_pool_kernel_edge_cases(tracer):
-    """The pooled persistent kernel on the shapes that stress its slot bookkeeping: fewer pixels than one warp's
+    """The pooled persistent kernel and the streaming kernel on the shapes that stress their slot bookkeeping: fewer pixels than one warp's
     pool, an image smaller than a tile, zero bounces, an empty scene, a frame whose pixel count is not a multiple
     of anything -- bit-identical to the megakernel every time."""
     scene = _scene(4, 60, 7)
@@ -482,7 +489,7 @@ def test_pool_kernel_edge_cases(tracer):
         for (w, h, spp, bounces, sc) in [(1, 1, 5, 4, scene), (7, 3, 4, 6, scene), (9, 9, 3, 0, scene), (67, 41, 2, 5, scene),
                                           (33, 17, 3, 4, empty), (130, 67, 1, 1, scene)]:
             imgs = []
-            for kernel in (0, 3):
+            for kernel in (0, 3, 4):
                 tracer.set_option("kernel", kernel)
                 tracer.set_camera(rtb.default_camera(w, h), w, h)
                 tracer.set_render_data(scene.render_settings(spp, bounces))
@@ -491,11 +498,86 @@ def test_pool_kernel_edge_cases(tracer):
                 f = tracer.render(img, 3, 77)
                 tracer.render(img, f, 78)
                 imgs.append(img)
-            assert (imgs[0] == imgs[1]).all(), (w, h, spp, bounces)
+            assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[2]).all(), (w, h, spp, bounces)
             assert np.isfinite(imgs[0]).all()
     finally:
         tracer.set_option("kernel", 2)
         tracer.setup(scene, 64, 48, 1, 3)
+
+
+def test_deep_tree_falls_back_to_a_bounded_hierarchy(tracer):
+    """150 nested spheres around one centre: PLOC merges one pair per round (the two innermost clusters are the only
+    mutual nearest neighbours), a tree ~150 levels high, more than the traversal stack holds.  The commit measures the
+    height, rebuilds with the Karras hierarchy (bounded by the code length) and the frame equals brute force; a
+    deeper-than-the-stack tree is never traversed (it used to drop far children silently)."""
+    lib = rtb.lib
+    mat = rtb.Material()
+    mat.type = 0
+    mat.texture.type = 0
+    mat.texture.colour = rtb.Vec3(0.7, 0.6, 0.5)
+    mat.smoothness = 0.3
+    try:
+        tracer.set_camera(rtb.default_camera(96, 64), 96, 64)
+        tracer.set_render_data(rtb.RenderData(2, 4, 1, rtb.Vec3(0.8, 1.0, 1.0)))
+        lib.rtb_scene_begin(tracer.ctx)
+        m = lib.rtb_scene_add_material(tracer.ctx, ctypes.byref(mat))
+        c = (ctypes.c_float * 3)(0.1, -0.05, 3.0)
+        for i in range(150):
+            assert lib.rtb_scene_add_sphere(tracer.ctx, c, ctypes.c_float(0.2 * 1.012 ** i), m) == i
+        tracer.set_option("large_split", 0)
+        assert lib.rtb_scene_commit(tracer.ctx) == 0, lib.rtb_last_error(tracer.ctx)
+        assert 1 <= tracer.info("tree_height") <= 94
+        imgs = []
+        for traversal in (0, 1):
+            tracer.set_option("traversal", traversal)
+            for kernel in (0, 1, 3, 4):
+                tracer.set_option("kernel", kernel)
+                img = np.zeros((64, 96, 3), np.float32)
+                tracer.render(img, 0, 11)
+                imgs.append(img)
+        for img in imgs[1:]:
+            assert (img == imgs[0]).all()
+        assert (imgs[0] != np.float32(0)).any()
+    finally:
+        tracer.set_option("traversal", 0)
+        tracer.set_option("kernel", 2)
+        tracer.set_option("large_split", 1)
+        tracer.setup(_scene(1, 0, 0), 64, 48, 1, 3)
+
+
+def test_non_finite_primitive_does_not_break_the_build(tracer):
+    """A triangle with a NaN vertex and a sphere with an infinite radius: the reference renders such a scene (the
+    primitives simply never hit, or hit everything); the tree build keeps its boxes finite instead of failing with
+    'unknown error', and the frame equals brute force over the same primitives."""
+    lib = rtb.lib
+    mat = rtb.Material()
+    mat.type = 0
+    mat.texture.type = 0
+    mat.texture.colour = rtb.Vec3(0.5, 0.5, 0.5)
+    try:
+        tracer.set_camera(rtb.default_camera(80, 60), 80, 60)
+        tracer.set_render_data(rtb.RenderData(2, 3, 1, rtb.Vec3(0.8, 1.0, 1.0)))
+        lib.rtb_scene_begin(tracer.ctx)
+        m = lib.rtb_scene_add_material(tracer.ctx, ctypes.byref(mat))
+        for k in range(6):
+            c = (ctypes.c_float * 3)(-1.0 + 0.4 * k, 0.0, 3.0)
+            lib.rtb_scene_add_sphere(tracer.ctx, c, ctypes.c_float(0.15), m)
+        nan = float("nan")
+        pts = (ctypes.c_float * 9)(0, 0, 2, nan, 1, 2, 1, 0, 2)
+        assert lib.rtb_scene_add_triangle(tracer.ctx, pts, None, m) >= 0
+        c = (ctypes.c_float * 3)(0, 5, 3)
+        assert lib.rtb_scene_add_sphere(tracer.ctx, c, ctypes.c_float(float("inf")), m) >= 0
+        assert lib.rtb_scene_commit(tracer.ctx) == 0, lib.rtb_last_error(tracer.ctx)
+        imgs = []
+        for traversal in (0, 1):
+            tracer.set_option("traversal", traversal)
+            img = np.zeros((60, 80, 3), np.float32)
+            tracer.render(img, 0, 3)
+            imgs.append(img)
+        assert np.array_equal(imgs[0], imgs[1], equal_nan=True)
+    finally:
+        tracer.set_option("traversal", 0)
+        tracer.setup(_scene(1, 0, 0), 64, 48, 1, 3)
 
 
 def test_bounce_limit_beyond_the_wavefront_packing(tracer):
@@ -514,7 +596,7 @@ def test_bounce_limit_beyond_the_wavefront_packing(tracer):
             assert int(tracer.info("kernel")) == 0
             imgs[kernel] = img
         assert (imgs[0] == imgs[2]).all() and np.isfinite(imgs[0]).all()
-        for kernel in (1, 3):
+        for kernel in (1, 3, 4):
             tracer.set_option("kernel", kernel)
             with pytest.raises(Exception, match="Error from CUDA"):
                 tracer.render(np.zeros((48, 64, 3), np.float32), 0, 7)

@@ -175,7 +175,7 @@ def test_c3_config_size_vs_reference_cuda():
     obj, sub, t = tr.primary_ids()
     mism = int((obj != r_obj).sum())
     imgs = {}
-    for kernel in (3, 1, 0):
+    for kernel in (4, 3, 1, 0):
         tr.set_option("kernel", kernel)
         img = np.zeros((C3H, C3W, 3), np.float32)
         tr.render(img, 0, 1000)
@@ -194,7 +194,7 @@ def test_c3_config_size_vs_reference_cuda():
         rec.update(strict_obj_mismatches=int((s_obj != n_obj).sum()), strict_t_mismatches=int((s_t != n_t).sum()))
         assert rec["strict_obj_mismatches"] == 0 and rec["strict_t_mismatches"] == 0
     tr.close()
-    assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[3]).all() and (imgs[0] == auto).all()
+    assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[3]).all() and (imgs[0] == imgs[4]).all() and (imgs[0] == auto).all()
     rmse = float(np.sqrt(((imgs[3] - r_img) ** 2).mean()))
     bad = int((np.abs(imgs[3] - r_img).max(axis=2) > 1e-5).sum())
     rec.update(rmse_8spp=rmse, pixels_differing=bad, bit_identical_floats=float((imgs[3] == r_img).mean()))
@@ -221,7 +221,7 @@ def test_c4_config_size_vs_reference_cuda():
     obj, sub, t = tr.primary_ids()
     mism = int((obj != r_obj).sum())
     imgs = {}
-    for kernel in (3, 1):
+    for kernel in (4, 3, 1):
         tr.set_option("kernel", kernel)
         img = np.zeros((C4H, C4W, 3), np.float32)
         tr.render(img, 0, 1000)
@@ -232,7 +232,7 @@ def test_c4_config_size_vs_reference_cuda():
     tr.render(part, 0, 1000)
     rows = rtb.shard_rows_host(C4H, 3, 8, 8)
     tr.close()
-    assert (imgs[3] == imgs[1]).all()
+    assert (imgs[3] == imgs[1]).all() and (imgs[4] == imgs[1]).all()
     assert (part[rows] == imgs[3][rows]).all()
     rmse = float(np.sqrt(((imgs[3] - r_img) ** 2).mean()))
     bad = int((np.abs(imgs[3] - r_img).max(axis=2) > 1e-5).sum())

@@ -60,3 +60,29 @@ if __name__ == "__main__":
             run("C3-32", {"kernel": k})
         run("C3-32", {"kernel": 3, "blocks_per_sm": 4}); run("C3-32", {"kernel": 3, "blocks_per_sm": 5})
         run("C4-8", {"kernel": 3}, 8); run("C4-8", {"kernel": 1}, 8); run("C2-16", {"kernel": 3})
+    elif which == "sah":
+        for name, share in (("C3-32", 1), ("C1", 1), ("C2-16", 1)):
+            for b, ls in ((1, 1), (2, 1), (2, 0), (1, 0), (0, 1)):
+                run(name, {"kernel": 1, "builder": b, "large_split": ls}, share)
+    elif which == "wf":
+        run("C3-32", {"kernel": 1}); run("C1", {"kernel": 1}); run("C4-8", {"kernel": 1}); run("C2-16", {"kernel": 0}); run("C5-16", {"kernel": 1})
+    elif which == "stream":
+        run("C3-32", {"kernel": 1})
+        for ns in (0, 48, 56, 64, 72):
+            sid, p0, p1, W, H, spp, bounces = CFG["C3-32"]
+            sc = rtb.Scene(sid, p0, p1)
+            tr = rtb.Tracer(0)
+            tr.set_option("kernel", 4)
+            if ns:
+                tr.set_option("stream_shade_sms", ns)
+            tr.setup(sc, W, H, spp, bounces)
+            ms = []
+            for k in range(6):
+                tr.reset(); tr.render_device(1, 100 + k); tr.sync(); ms.append(round(tr.device_ms(), 2))
+            print(json.dumps(dict(name="C3-32", kernel=4, shade_sms_opt=ns, ms=ms, shade_sms=tr.info("stream_shade_sms"),
+                                  util_shade=round(tr.info("stream_util_shade"), 3), util_trav=round(tr.info("stream_util_traverse"), 3),
+                                  slots=tr.info("stream_slots"))), flush=True)
+            tr.close()
+        for name, share in (("C3-32", 8), ("C4-8", 1), ("C4-8", 8), ("C2-16", 1), ("C1", 1), ("C5-16", 1)):
+            run(name, {"kernel": 4}, share, reps=6)
+            run(name, {}, share, reps=3)
