@@ -447,19 +447,18 @@ def c4_tiles_record(args, rank, world, local_rank, dist):
     with the image gathered over NCCL), measured in THIS run at THIS world size next to the headline: the 1-GPU line
     is the denominator of the N = 2/4/8 lines.  16 spp per step (of the config's 1024: a rate)."""
     import math
+    note("c4: building the job")
     job = Job(args, "C4", "tiles", rank, world, local_rank, dist)
+    note("c4: job ready:", job.sharding_desc())
     cnt = job.count()
+    note("c4: counted", cnt["segments"])
     with job.torch.cuda.stream(job.ext):
         for k in range(3):
             job.device_step(k)
     ms_warm, _, _, _ = job.timed(2)
-    # >= 5 s timed: >= 20 clock samples at 200 ms (a 100 ms nvidia-smi loop slowed the launch-heavy frames by 20 %)
+    # >= 5 s timed: >= 20 clock samples at 200 ms
     steps = max(5, min(600, int(math.ceil(5200.0 / max(ms_warm, 1e-3)))))
-    # The host waits for each step before it enqueues the next (the wait is inside the timed region): with tens of
-    # these 560-launch frames enqueued back to back every frame ran 18 % slower on the device (175 ms instead of 148 ms
-    # at N = 1, measured with and without the clock sampler, with the run-ahead bounded to 1-3 frames or not:
-    # tools/c4_probe.py), while frames the host waits for run at 148 ms for as long as one likes.
-    ms_step, kernel_ms, launches, clocks = job.timed(steps, sample_ms=200, sync_each_step=True)
+    ms_step, kernel_ms, launches, clocks = job.timed(steps, sample_ms=200)
     kind, kdesc, tuned = job.kernel_desc()
     rec = None
     if rank == 0:
@@ -471,6 +470,12 @@ def c4_tiles_record(args, rank, world, local_rank, dist):
                "op_mix_per_ray": {"box": cnt["box_tests"] / cnt["segments"], "tri": cnt["tri_tests"] / cnt["segments"]}}
     job.close()
     return rec
+
+
+def note(*a):
+    """progress notes on stderr (RTB_BENCH_VERBOSE=1)"""
+    if os.environ.get("RTB_BENCH_VERBOSE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} t={time.perf_counter():.1f}]", *a, file=sys.stderr, flush=True)
 
 
 def main():
@@ -510,7 +515,9 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    note("building the job")
     job = Job(args, args.workload, args.sharding, rank, world, local_rank, dist)
+    note("job ready:", job.sharding_desc())
     tr, W, H, spp = job.tr, job.W, job.H, job.spp
     cnt = job.count()
     rays_per_step = cnt["segments"]
@@ -519,7 +526,9 @@ def main():
             job.device_step(k)
     # with option "kernel" = 2 (the default) the first warm-up frame timed the variants on this rank's share of the
     # workload and kept the fastest; from here on the choice is fixed
+    note("warm-up done")
     ms_step, kernel_ms, launches, clocks = job.timed(args.steps)
+    note("timed:", ms_step)
     kernel_kind, kernel_desc, tuned = job.kernel_desc()
 
     # ---- end to end through the reference-facing entry point, host buffers ----
@@ -548,11 +557,14 @@ def main():
     info = {k: tr.info(k) for k in ("builder", "num_prims", "build_ms")}
     sharding_desc = job.sharding_desc()
     slices = job.slices
+    note("e2e done")
     job.close()
+    note("job closed")
 
     c4 = None
     if args.workload == "C3" and not args.no_c4_tiles:
         c4 = c4_tiles_record(args, rank, world, local_rank, dist)
+    note("c4 record done")
 
     if rank == 0:
         value = rays_per_step / ms_step / 1e3                       # Mrays/s, whole job

@@ -51,7 +51,9 @@ struct rtb_ctx {
     bool timing_pending = false;
     cudaEvent_t frame_done[4] = {nullptr, nullptr, nullptr, nullptr};  // end of the last frames (bounded run-ahead)
     long long frames_enqueued = 0;
-    int opt_run_ahead = 2;
+    int opt_run_ahead = 0;
+    cudaEvent_t pace_events[2][64] = {};   // wavefront loop: per stream, one event every 8 iterations (bounded run-ahead)
+    int opt_wf_pace = 0;
 
     // wavefront variant: per-pixel records, two queues, counters {n[0], n[1], fetch}
     float4 *d_wf_state = nullptr;

@@ -250,13 +250,26 @@ __device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, 
     }
 }
 
+// A ray with a NaN in its origin or direction hits nothing in the reference: Triangle::hit gets a NaN determinant and
+// fails `u >= 0` (objects.cu:141-152), Sphere::hit a NaN discriminant and fails `disc >= 0` (:52-55); quads and cuboids
+// are triangles.  Such rays exist: Box-Muller with u2 == 0 gives rho = inf (utils.cu:236-238, one draw in 2^32), the
+// normalisation turns it into NaN, and the path keeps that NaN for its remaining bounces.  The conservative box test
+// drops NaNs, i.e. ACCEPTS every box, so without this check one such ray walks the whole tree: a 1 M-triangle scene
+// showed one 1.2 s frame in forty (measured: tools/c4_probe.py).  The tree is skipped; the result (a miss) is the same.
+__device__ __forceinline__ bool ray_has_nan(const Ray &r) {
+    // x * 0 is NaN for a NaN or infinite x (an infinite coordinate misses everything as well: the barycentrics or the
+    // discriminant become inf - inf), 0 otherwise
+    float s = r.o.x * 0.f + r.o.y * 0.f + r.o.z * 0.f + r.d.x * 0.f + r.d.y * 0.f + r.d.z * 0.f;
+    return s != s;
+}
+
 // The root's node step, taken with the node in the kernel parameters (uniform loads, no L1
 // traffic) by the kernel that creates the ray, where the whole warp is converged.  Returns the
 // child to start at (`first`; RTB_DONE = the ray cannot touch the tree closer than `best`) and the
 // child to visit afterwards (`second`, 0 = none).
 __device__ __forceinline__ void root_step(const DScene &s, const Ray &r, const Best &best, int &first, int &second, Counters &cnt) {
     first = RTB_DONE; second = 0;
-    if (s.num_bvh_prims <= 0) return;
+    if (s.num_bvh_prims <= 0 || ray_has_nan(r)) return;
     if (s.root_ref < 0) { first = s.root_ref; return; }  // a one-primitive tree: the root is a leaf
     float limit = best.t * 1.0001f, n0, n1;
     RTB_COUNT(cnt, box); RTB_COUNT(cnt, box);
@@ -298,6 +311,7 @@ __device__ __forceinline__ void trav_start(const DScene &s, Trav &T) {
 __device__ __forceinline__ void trav_begin(const DScene &s, const Ray &r, Trav &T, unsigned mask, Counters &cnt) {
     large_prims_best(s, r, T.best, mask, cnt);
     trav_start(s, T);
+    if (ray_has_nan(r)) { T.cur = RTB_DONE; T.leaf = 0; }  // hits nothing (see ray_has_nan): do not walk the tree
 }
 
 // Advance the rays of the warp through the LBVH: warp-synchronous "while-while" traversal with

@@ -580,6 +580,39 @@ def test_non_finite_primitive_does_not_break_the_build(tracer):
         tracer.setup(_scene(1, 0, 0), 64, 48, 1, 3)
 
 
+def test_nan_rays_skip_the_tree_and_still_match_brute_force(tracer):
+    """A ray with a NaN coordinate hits nothing in the reference (NaN determinant / discriminant); the conservative box
+    test would accept every box for it, so the traversal cuts such rays short (ray_has_nan).  A camera at a NaN / an
+    infinite position makes every primary ray one of them: ids, distances and frames equal brute force, which runs the
+    reference's primitive tests on every primitive."""
+    scene = _scene(0, 0, 0)
+    try:
+        for bad in (float("nan"), float("inf")):
+            cam = rtb.default_camera(96, 64)
+            cam.cam_pos.x = bad
+            res = []
+            for traversal in (0, 1):
+                tracer.set_option("traversal", traversal)
+                tracer.set_camera(cam, 96, 64)
+                tracer.set_render_data(scene.render_settings(2, 4))
+                tracer.set_scene(scene)
+                obj, sub, t = tracer.primary_ids()
+                imgs = []
+                for kernel in (0, 1, 3, 4):
+                    tracer.set_option("kernel", kernel)
+                    img = np.zeros((64, 96, 3), np.float32)
+                    tracer.render(img, 0, 9)
+                    imgs.append(img)
+                assert all(np.array_equal(im, imgs[0], equal_nan=True) for im in imgs[1:])
+                res.append((obj, t, imgs[0]))
+            assert (res[0][0] == -1).all() and (res[1][0] == -1).all()
+            assert (res[0][1] == res[1][1]).all() and np.array_equal(res[0][2], res[1][2], equal_nan=True)
+    finally:
+        tracer.set_option("traversal", 0)
+        tracer.set_option("kernel", 2)
+        tracer.setup(_scene(1, 0, 0), 64, 48, 1, 3)
+
+
 def test_bounce_limit_beyond_the_wavefront_packing(tracer):
     """The reference has no upper bound on reflection_limit (src/raytracer.cu:72); the wavefront kernels pack the
     bounce index in 8 bits.  With the automatic kernel choice (the default) a limit of 300 renders through the
