@@ -249,6 +249,17 @@ void rtb_destroy_multi(rtb_ctx **ctxs, int n);
  * reference's `<=` rule or -1; sub_id = triangle inside it (mesh: triangle index; quad 0/1;
  * cuboid face*2+{0,1}; else 0); t = distance (INF = 2^30 on a miss).  HOST buffers, width*height. */
 int rtb_primary_ids(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
+/* rtb_primary_ids for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation).  No counterpart in the reference.
+ * Same kernel, same arguments and results as rtb_primary_ids (buffers may be host or device memory; t may be
+ * NULL), but the kernel's device-side staging planes live in a static device array of the library instead of
+ * per-call cudaMalloc'ed buffers: the call allocates nothing.  Limit: width * height <= RTB_NOALLOC_MAX_PIXELS
+ * (2 Mi pixels: 1920 x 1080 fits, 3840 x 2160 does not; 24 MiB held by every GPU that loads the library until the
+ * process exits); a larger image is refused with an error that says so.  All calls on one GPU share the array:
+ * calls that overlap on the GPU (two contexts of one device, two host threads) race -- serialise them. */
+#define RTB_NOALLOC_MAX_PIXELS (2 * 1024 * 1024)
+int rtb_primary_ids_noalloc(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
+int rtb_noalloc_max_pixels(void);
 /* counters of the last render when option "counters" = 1 */
 int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
 /* options: "counters" 0/1; "traversal" 0 = LBVH, 1 = brute force over the flattened primitives;

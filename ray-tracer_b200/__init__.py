@@ -81,6 +81,8 @@ lib.rtb_shard_row_count.argtypes = [_i, _i, _i, _i]
 lib.rtb_shard_pack.argtypes = [_vp, _vp]
 lib.rtb_shard_unpack.argtypes = [_vp, _vp]
 lib.rtb_primary_ids.argtypes = [_vp, _vp, _vp, _vp]
+lib.rtb_primary_ids_noalloc.argtypes = [_vp, _vp, _vp, _vp]
+lib.rtb_noalloc_max_pixels.argtypes = []
 lib.rtb_counters.argtypes = [_vp, ctypes.POINTER(Counters)]
 lib.rtb_set_option.argtypes = [_vp, ctypes.c_char_p, _i]
 lib.rtb_get_info.argtypes = [_vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
@@ -343,6 +345,15 @@ class Tracer:
         n = self.width * self.height
         obj, sub, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
         self._check(lib.rtb_primary_ids(self.ctx, _ptr(obj), _ptr(sub), _ptr(t)))
+        shape = (self.height, self.width)
+        return obj.reshape(shape), sub.reshape(shape), t.reshape(shape)
+
+    def primary_ids_noalloc(self):
+        """rtb_primary_ids_noalloc: the same pass with the staging planes in the library's static device array (no
+        cudaMalloc in the call); refused beyond rtb_noalloc_max_pixels()"""
+        n = self.width * self.height
+        obj, sub, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        self._check(lib.rtb_primary_ids_noalloc(self.ctx, _ptr(obj), _ptr(sub), _ptr(t)))
         shape = (self.height, self.width)
         return obj.reshape(shape), sub.reshape(shape), t.reshape(shape)
 
