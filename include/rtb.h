@@ -260,18 +260,36 @@ int rtb_primary_ids(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
 #define RTB_NOALLOC_MAX_PIXELS (2 * 1024 * 1024)
 int rtb_primary_ids_noalloc(rtb_ctx *ctx, int32_t *obj_id, int32_t *sub_id, float *t);
 int rtb_noalloc_max_pixels(void);
+/* Test hook (no counterpart in the reference): the reference's BVH partition of one mesh (which triangles share which
+ * box, src/objects.cu:602-770) computed by the host restatement (on_device = 0) or by the device version that
+ * rtb_scene_commit uses for big meshes (on_device = 1; option "device_flatten").  tri_points: 9 floats per triangle.
+ * Out: leaf_of[n] node index of each triangle's leaf, degenerate[n] 1 where that leaf's box is flat on an axis,
+ * nodes[8 * nodes_cap] = {lo.xyz, parent, hi.xyz, 0} per node in the reference's preorder numbering. */
+int rtb_debug_mesh_partition(int device, const float *tri_points, int n, int on_device, int32_t *leaf_of, uint8_t *degenerate, float *nodes,
+                             int nodes_cap, int *num_nodes);
 /* counters of the last render when option "counters" = 1 */
 int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
 /* options: "counters" 0/1; "traversal" 0 = LBVH, 1 = brute force over the flattened primitives;
- * "kernel" 0 = persistent megakernel, 1 = wavefront, 3 = pooled persistent kernel (one launch per frame, per-warp
- * pools of 64 pixel slots), 2 = timed choice between them at the first frame (default; bit-identical images;
- * beyond the packing limits of kernels 1 and 3 -- reflection_limit > 255 or rays_per_pixel >= 2^24 -- the choice
- * is the megakernel, while pinning 1 or 3 refuses such a frame);
- * "strict_fp" 0/1 (kernels built with -fmad=false); "builder" 0 = Karras LBVH, 1 = PLOC (next commit);
+ * "kernel" 0 = persistent megakernel, 1 = wavefront pair, 3 = pooled persistent kernel (one launch per frame,
+ * per-warp pools of 64 pixel slots), 4 = streaming kernel (one launch per frame, SMs specialised as shade /
+ * traverse, ticket queues; "stream_slots", "stream_shade_sms" shape it), 2 = timed choice at the first frame
+ * (default; bit-identical images; beyond the packing limits of kernels 1, 3, 4 -- reflection_limit > 255 or
+ * rays_per_pixel >= 2^24 -- the choice is the megakernel, while pinning 1, 3 or 4 refuses such a frame);
+ * "tune_set" (kernels the timed choice tries: 1 megakernel | 2 wavefront | 8 pooled | 16 streaming; default 3);
+ * "strict_fp" 0/1 (kernels built with -fmad=false); "builder" 0 = Karras LBVH, 1 = PLOC (next commit; 2 = host
+ * full-sweep SAH, a tree-quality yardstick for experiments only); "ploc_radius"; "device_flatten" 0 = meshes are
+ * partitioned + flattened on the host, 1 = on the device, 2 = on the device from 32768 triangles up (default; next
+ * commit; same arrays either way);
  * "large_split", "max_large", "reference_bvh_quirks" (next commit); "walk_min", "refill", "wf_refill",
  * "wf_rebuild", "wf_groups", "wf_streams" (traversal / wavefront policy, 0 = tuned); "block_threads";
- * "blocks_per_sm"; "tune_set" (kernels the timed choice tries: 1 megakernel | 2 wavefront | 8 pooled);
- * "exchange" 0/1/2 and "slices" 0/1 (multi-GPU section above).  Every change re-arms the timed choice. */
+ * "blocks_per_sm"; "wf_timing" (events around every wavefront launch of the next frame);
+ * "run_ahead" (frames the host may enqueue ahead of the device, 0 = unbounded) and "wf_pace" (wavefront
+ * iterations the host may run ahead, 0 = unbounded): host pacing knobs, measured without effect, off by default;
+ * "exchange" 0/1/2 and "slices" 0/1 (multi-GPU section above).  A change of kernel-shaping options re-arms the
+ * timed choice; a re-commit keeps it unless the primitive count changed by more than 2x.
+ * info keys (rtb_get_info): "num_prims", "num_nodes", "tree_height", "build_ms", "commit_ms",
+ * "commit_partition_ms", "commit_flatten_ms", "commit_upload_ms", "scene_bytes", "culled_tris", "kernel",
+ * "tune_*_ms", "wf_*_ms", "exchange", "exchange_fused", "comm_world", "stream_*" (see rtb_api.cu). */
 int rtb_set_option(rtb_ctx *ctx, const char *key, int value);
 int rtb_get_info(rtb_ctx *ctx, const char *key, double *value);
 /* sustained FP32 FMA throughput of the device (TFLOP/s, dependent-chain FFMA microbenchmark over

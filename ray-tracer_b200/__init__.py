@@ -83,6 +83,7 @@ lib.rtb_shard_unpack.argtypes = [_vp, _vp]
 lib.rtb_primary_ids.argtypes = [_vp, _vp, _vp, _vp]
 lib.rtb_primary_ids_noalloc.argtypes = [_vp, _vp, _vp, _vp]
 lib.rtb_noalloc_max_pixels.argtypes = []
+lib.rtb_debug_mesh_partition.argtypes = [_i, _vp, _i, _i, _vp, _vp, _vp, _i, _ip]
 lib.rtb_counters.argtypes = [_vp, ctypes.POINTER(Counters)]
 lib.rtb_set_option.argtypes = [_vp, ctypes.c_char_p, _i]
 lib.rtb_get_info.argtypes = [_vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
@@ -159,7 +160,7 @@ class Scene:
         return rd
 
     def __del__(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and scenes_lib is not None:   # module globals are gone at interpreter shutdown
             scenes_lib.rtbs_free(self.handle)
             self.handle = None
 

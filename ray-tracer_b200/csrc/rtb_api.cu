@@ -6,9 +6,11 @@
 #include "rtb_ctx.h"
 #include "rtb_lbvh.h"
 #include "rtb_refbvh.h"
+#include "rtb_meshprep.h"
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include <chrono>
@@ -45,6 +47,20 @@ template <typename T> cudaError_t upload(rtb_ctx *c, const std::vector<T> &v, co
     return e;
 }
 
+// device array of `total` elements (at least one) whose first v.size() come from the host
+template <typename T> cudaError_t upload_front(rtb_ctx *c, const std::vector<T> &v, size_t total, T **out) {
+    *out = nullptr;
+    size_t bytes = sizeof(T) * (total == 0 ? 1 : total);
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    c->scene_allocs.push_back(p);
+    c->scene_bytes += bytes;
+    if (!v.empty()) e = cudaMemcpyAsync(p, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice, c->stream);
+    *out = (T *)p;
+    return e;
+}
+
 // ---- host float helpers: the expressions of Triangle::precompute (objects.cu:175-186) ----------
 struct H3 {
     float x, y, z;
@@ -74,7 +90,35 @@ TriRec make_tri(H3 p0, H3 p1, H3 p2) {
     return t;
 }
 
+// a mesh whose partition and records are made on the device (rtb_meshprep.cu): its triangles come after all host-built
+// ones in the scene arrays
+struct DevMesh {
+    int obj = 0, n = 0, node_base = -1;
+    float *d_pts = nullptr, *d_uv = nullptr;
+    MeshPrep prep;
+    size_t tri_base = 0, leaf_base = 0;
+};
+
+// the vertices of the triangles as their records give them back, NaN-skipping min / max (fminf / fmaxf written out:
+// libm calls otherwise, 18 per triangle)
+void rec_box(const float4 *rec, int count, float *blo, float *bhi) {
+    for (int c = 0; c < 3; c++) { blo[c] = 3e38f; bhi[c] = -3e38f; }
+    for (int k = 0; k < count; k++) {
+        float4 a = rec[3 * k], b = rec[3 * k + 1], cc = rec[3 * k + 2];
+        float p[3][3] = {{a.x, a.y, a.z}, {a.x + a.w, a.y + b.x, a.z + b.y}, {a.x + b.z, a.y + b.w, a.z + cc.x}};
+        for (int v = 0; v < 3; v++)
+            for (int c = 0; c < 3; c++) {
+                blo[c] = (blo[c] < p[v][c] || p[v][c] != p[v][c]) ? blo[c] : p[v][c];
+                bhi[c] = (bhi[c] > p[v][c] || p[v][c] != p[v][c]) ? bhi[c] : p[v][c];
+            }
+    }
+}
+
 struct Flat {
+    std::vector<DevMesh> dev_meshes;
+    ~Flat() {
+        for (DevMesh &m : dev_meshes) { cudaFree(m.d_pts); cudaFree(m.d_uv); m.prep.release(); }
+    }
     std::vector<float4> tris, spheres, ref_nodes;
     std::vector<int2> tri_ids;
     std::vector<float2> tri_uv;
@@ -97,18 +141,7 @@ struct Flat {
         for (int c = 0; c < 3; c++) leaf_box.push_back(blo[c]);
         for (int c = 0; c < 3; c++) leaf_box.push_back(bhi[c]);
     }
-    void tri_box(int idx, int count, float *blo, float *bhi) const {
-        for (int c = 0; c < 3; c++) { blo[c] = 3e38f; bhi[c] = -3e38f; }
-        for (int k = 0; k < count; k++) {
-            float4 a = tris[3 * (idx + k)], b = tris[3 * (idx + k) + 1], cc = tris[3 * (idx + k) + 2];
-            float p[3][3] = {{a.x, a.y, a.z}, {a.x + a.w, a.y + b.x, a.z + b.y}, {a.x + b.z, a.y + b.w, a.z + cc.x}};
-            for (int v = 0; v < 3; v++)
-                for (int c = 0; c < 3; c++) {  // fminf / fmaxf written out: libm calls otherwise, 18 per triangle
-                    blo[c] = (blo[c] < p[v][c] || p[v][c] != p[v][c]) ? blo[c] : p[v][c];
-                    bhi[c] = (bhi[c] > p[v][c] || p[v][c] != p[v][c]) ? bhi[c] : p[v][c];
-                }
-        }
-    }
+    void tri_box(int idx, int count, float *blo, float *bhi) const { rec_box(&tris[3 * (size_t)idx], count, blo, bhi); }
 
     int push_tri(TriRec t, int obj, int sub, const float *uv, int refleaf) {
         int idx = (int)tri_ids.size();
@@ -287,10 +320,50 @@ int flatten(rtb_ctx *c, Flat &f) {
                 if (o.tri_first < 0 || o.tri_count < 0 || (size_t)(o.tri_first + o.tri_count) * 9 > c->tri_points.size())
                     return fail(c, "flattening scene", "mesh triangle range out of bounds");
                 const float *pts = c->tri_points.data() + (size_t)o.tri_first * 9;
-                RefBvh rb;
                 int node_base = (int)(f.ref_nodes.size() / 2);
+                // a big mesh is partitioned and flattened on the device (rtb_meshprep.cu; option "device_flatten":
+                // 0 never, 1 every mesh, 2 = from 32768 triangles up); non-finite coordinates take the host path
+                if (o.tri_count > 0 && c->opt_builder != 2 && (c->opt_device_flatten == 1 || (c->opt_device_flatten == 2 && o.tri_count >= 32768))) {
+                    auto tp0 = std::chrono::steady_clock::now();
+                    f.dev_meshes.emplace_back();
+                    DevMesh &m = f.dev_meshes.back();
+                    m.obj = i; m.n = o.tri_count;
+                    size_t pts_bytes = sizeof(float) * 9 * (size_t)o.tri_count;
+                    RTB_CUDA(c, cudaMalloc((void **)&m.d_pts, pts_bytes), "allocating mesh vertices");
+                    RTB_CUDA(c, cudaMemcpyAsync(m.d_pts, pts, pts_bytes, cudaMemcpyHostToDevice, c->stream), "uploading mesh vertices");
+                    if (c->mesh_uv_given && !c->tri_uv.empty()) {
+                        size_t uv_bytes = sizeof(float) * 6 * (size_t)o.tri_count;
+                        RTB_CUDA(c, cudaMalloc((void **)&m.d_uv, uv_bytes), "allocating mesh texture points");
+                        RTB_CUDA(c, cudaMemcpyAsync(m.d_uv, c->tri_uv.data() + (size_t)o.tri_first * 6, uv_bytes, cudaMemcpyHostToDevice, c->stream), "uploading mesh texture points");
+                    }
+                    int nonfinite = 0;
+                    m.prep.n = o.tri_count; m.prep.kept = o.tri_count;
+                    if (c->opt_ref_quirks) RTB_CUDA(c, mesh_partition_device(m.d_pts, o.tri_count, c->stream, m.prep, &nonfinite), "partitioning the mesh");
+                    c->commit_partition_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+                    if (!nonfinite) {
+                        if (c->opt_ref_quirks) {
+                            m.node_base = node_base;
+                            for (size_t q = 0; q < m.prep.nodes.size(); q += 2) {
+                                float4 lo = m.prep.nodes[q];
+                                int parent;
+                                std::memcpy(&parent, &lo.w, sizeof(int));
+                                parent = parent < 0 ? -1 : node_base + parent;
+                                std::memcpy(&lo.w, &parent, sizeof(int));
+                                f.ref_nodes.push_back(lo);
+                                f.ref_nodes.push_back(m.prep.nodes[q + 1]);
+                            }
+                        }
+                        f.culled += o.tri_count - m.prep.kept;
+                        break;
+                    }
+                    cudaFree(m.d_pts); cudaFree(m.d_uv); m.prep.release();
+                    f.dev_meshes.pop_back();
+                }
+                RefBvh rb;
                 if (c->opt_ref_quirks) {
+                    auto tp0 = std::chrono::steady_clock::now();
                     ref_bvh_partition(pts, o.tri_count, rb);
+                    c->commit_partition_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
                     for (const RefBvhNode &n : rb.nodes) {
                         int parent = n.parent < 0 ? -1 : node_base + n.parent;
                         float4 lo = make_float4(n.lo[0], n.lo[1], n.lo[2], 0.f);
@@ -991,6 +1064,12 @@ int rtb_create(rtb_ctx **out, int device) {
         return 1;
     }
     c->num_sms = prop.multiProcessorCount;
+    // RTB_DEVICE_FLATTEN = 0 / 1 / 2 presets option "device_flatten" (the GPU test suite runs once with 1: every mesh
+    // of every parity scene then goes through the device partition + flatten)
+    if (const char *env = std::getenv("RTB_DEVICE_FLATTEN")) {
+        int v = std::atoi(env);
+        if (v >= 0 && v <= 2) c->opt_device_flatten = v;
+    }
     *out = c;
     return 0;
 }
@@ -1054,6 +1133,7 @@ int rtb_scene_begin(rtb_ctx *c) {
     free_scene(c);
     c->objects.clear(); c->materials.clear(); c->tri_points.clear(); c->tri_uv.clear();
     c->image_data.clear(); c->images.clear();
+    c->mesh_uv_given = false;
     return 0;
 }
 
@@ -1123,6 +1203,7 @@ int rtb_scene_add_mesh(rtb_ctx *c, const float *tri_points, const float *tri_uv,
     int idx = add_object(c, o);
     if (idx < 0) return idx;
     c->tri_points.insert(c->tri_points.end(), tri_points, tri_points + (size_t)num_tris * 9);
+    if (tri_uv) c->mesh_uv_given = true;
     if (tri_uv) c->tri_uv.insert(c->tri_uv.end(), tri_uv, tri_uv + (size_t)num_tris * 6);
     else c->tri_uv.insert(c->tri_uv.end(), (size_t)num_tris * 6, 0.f);
     return idx;
@@ -1150,6 +1231,7 @@ int rtb_scene_update_mesh(rtb_ctx *c, int index, const float *tri_points, const 
     if (index < 0 || index >= (int)c->objects.size() || c->objects[index].type != RTB_OBJ_MESH) return fail(c, "rtb_scene_update_mesh", "not a mesh object");
     const RtbObject &o = c->objects[index];
     std::memcpy(&c->tri_points[(size_t)o.tri_first * 9], tri_points, (size_t)o.tri_count * 9 * sizeof(float));
+    if (tri_uv) c->mesh_uv_given = true;
     if (tri_uv) std::memcpy(&c->tri_uv[(size_t)o.tri_first * 6], tri_uv, (size_t)o.tri_count * 6 * sizeof(float));
     return 0;
 }
@@ -1169,95 +1251,213 @@ static int scene_commit_timed(rtb_ctx *c) {
     cudaStreamSynchronize(c->stream);
     free_scene(c);
     Flat f;
+    auto tf0 = std::chrono::steady_clock::now();
+    c->commit_partition_ms = 0;
     if (flatten(c, f) != 0) return 1;
+    auto tf1 = std::chrono::steady_clock::now();
+    c->commit_flatten_ms = std::chrono::duration<double, std::milli>(tf1 - tf0).count();
     DScene d{};
-    RTB_CUDA(c, upload(c, f.tris, &d.tris), "uploading triangles");
-    RTB_CUDA(c, upload(c, f.tri_ids, &d.tri_ids), "uploading triangle ids");
-    RTB_CUDA(c, upload(c, f.tri_uv, &d.tri_uv), "uploading triangle uvs");
-    RTB_CUDA(c, upload(c, f.tri_refleaf, &d.tri_refleaf), "uploading reference leaves");
+    // device-flattened meshes come after all host-built records
+    const size_t host_tris = f.tri_ids.size(), host_leaves = f.leaf_refs.size();
+    size_t dev_kept = 0;
+    for (DevMesh &m : f.dev_meshes) { m.tri_base = host_tris + dev_kept; m.leaf_base = host_leaves + dev_kept; dev_kept += (size_t)m.prep.kept; }
+    const size_t total_tris = host_tris + dev_kept, total_leaves = host_leaves + dev_kept;
+    if (total_tris > (size_t)(0x7fffffff >> RTB_KIND_BITS)) return fail(c, "flattening scene", "too many triangles for the leaf encoding");
+    float4 *w_tris = nullptr;
+    int2 *w_tri_ids = nullptr;
+    float2 *w_tri_uv = nullptr;
+    int *w_tri_refleaf = nullptr, *w_all_refs = nullptr;
+    RTB_CUDA(c, upload_front(c, f.tris, 3 * total_tris, &w_tris), "uploading triangles");
+    RTB_CUDA(c, upload_front(c, f.tri_ids, total_tris, &w_tri_ids), "uploading triangle ids");
+    RTB_CUDA(c, upload_front(c, f.tri_uv, 3 * total_tris, &w_tri_uv), "uploading triangle uvs");
+    RTB_CUDA(c, upload_front(c, f.tri_refleaf, total_tris, &w_tri_refleaf), "uploading reference leaves");
+    RTB_CUDA(c, upload_front(c, f.leaf_refs, total_leaves, &w_all_refs), "uploading primitive list");
+    d.tris = w_tris; d.tri_ids = w_tri_ids; d.tri_uv = w_tri_uv; d.tri_refleaf = w_tri_refleaf; d.all_refs = w_all_refs;
     RTB_CUDA(c, upload(c, f.spheres, &d.spheres), "uploading spheres");
     RTB_CUDA(c, upload(c, f.sphere_ids, &d.sphere_ids), "uploading sphere ids");
     RTB_CUDA(c, upload(c, f.obj_material, &d.obj_material), "uploading object materials");
     RTB_CUDA(c, upload(c, f.materials, &d.materials), "uploading materials");
     RTB_CUDA(c, upload(c, f.image_rgb, &d.image_rgb), "uploading texture rgb values");
     RTB_CUDA(c, upload(c, f.ref_nodes, &d.ref_nodes), "uploading reference boxes");
-    RTB_CUDA(c, upload(c, f.leaf_refs, &d.all_refs), "uploading primitive list");
-    d.num_prims = (int)f.leaf_refs.size();
+    int *d_scratch = nullptr;  // [0..5] bounds of the device meshes, [6] candidate count, [8..] candidates (int2)
+    constexpr int CAND_CAP = 256;
+    struct ScratchGuard { int *&p; ~ScratchGuard() { cudaFree(p); } } scratch_guard{d_scratch};
+    if (!f.dev_meshes.empty()) {
+        RTB_CUDA(c, cudaMalloc((void **)&d_scratch, sizeof(int) * (8 + 2 * CAND_CAP)), "allocating flatten scratch");
+        mesh_bounds_init(d_scratch, c->stream);
+        for (DevMesh &m : f.dev_meshes) {
+            MeshFill mf;
+            mf.d_pts = m.d_pts; mf.d_uv = m.d_uv; mf.n = m.n;
+            mf.d_slot = m.prep.d_slot; mf.d_leaf_of = m.prep.d_leaf_of;
+            mf.obj = m.obj; mf.tri_base = (int)m.tri_base; mf.leaf_base = (int)m.leaf_base; mf.node_base = m.node_base;
+            mf.tris = w_tris; mf.tri_ids = w_tri_ids; mf.tri_uv = w_tri_uv; mf.tri_refleaf = w_tri_refleaf; mf.leaf_refs = w_all_refs;
+            mf.bounds = d_scratch;
+            RTB_CUDA(c, mesh_fill_device(mf, c->stream), "flattening the mesh");
+        }
+        int hb[6];
+        RTB_CUDA(c, cudaMemcpyAsync(hb, d_scratch, sizeof hb, cudaMemcpyDeviceToHost, c->stream), "reading mesh bounds");
+        RTB_CUDA(c, cudaStreamSynchronize(c->stream), "flattening the mesh");
+        if (dev_kept > 0) {
+            float blo[3], bhi[3];
+            mesh_bounds_decode(hb, blo, bhi);
+            for (int a = 0; a < 3; a++) {
+                if (blo[a] < f.lo[a]) f.lo[a] = blo[a];
+                if (bhi[a] > f.hi[a]) f.hi[a] = bhi[a];
+            }
+        }
+        for (DevMesh &m : f.dev_meshes) {  // the inputs are no longer needed
+            cudaFree(m.d_pts); cudaFree(m.d_uv); m.prep.release();
+            m.d_pts = nullptr; m.d_uv = nullptr;
+        }
+    }
+    c->commit_upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tf1).count();
+    d.num_prims = (int)total_leaves;
     // large-primitive split: a leaf whose box area exceeds 1/20 of the scene box's is tested in the
     // warp-uniform list instead of living in the tree (at most RTB_MAX_LARGE, the largest first)
-    std::vector<int> large, small, small_idx;  // small_idx: position of each tree primitive in f.leaf_refs / f.leaf_box
-    if (c->opt_large_split && !f.leaf_refs.empty()) {
+    struct LargeCand {
+        float area;
+        long long order;   // position of the leaf in the primitive list (creation order; device meshes last)
+        int ref;
+        int mesh;          // device mesh it belongs to, -1 = a host-built leaf
+        float box[6];
+        float4 rec[6];     // records of its one or two triangles
+    };
+    std::vector<LargeCand> cands;
+    if (c->opt_large_split && total_leaves > 0) {
         float e[3] = {f.hi[0] - f.lo[0], f.hi[1] - f.lo[1], f.hi[2] - f.lo[2]};
         float scene_area = 2.f * (e[0] * e[1] + e[1] * e[2] + e[2] * e[0]);
-        std::vector<std::pair<float, int>> cand;
-        for (size_t i = 0; i < f.leaf_refs.size(); i++)
-            if (f.leaf_area[i] > 0.05f * scene_area) cand.push_back({-f.leaf_area[i], (int)i});
-        std::sort(cand.begin(), cand.end());
-        if ((int)cand.size() > std::min(c->opt_max_large, 32)) cand.resize(std::max(0, std::min(c->opt_max_large, 32)));  // bit masks of 32
-        std::vector<char> is_large(f.leaf_refs.size(), 0);
-        for (auto &pr : cand) is_large[pr.second] = 1;
-        for (size_t i = 0; i < f.leaf_refs.size(); i++) {
-            (is_large[i] ? large : small).push_back(f.leaf_refs[i]);
-            if (!is_large[i]) small_idx.push_back((int)i);
+        const float threshold = 0.05f * scene_area;
+        for (size_t i = 0; i < host_leaves; i++)
+            if (f.leaf_area[i] > threshold) {
+                LargeCand lc{};
+                lc.area = f.leaf_area[i]; lc.order = (long long)i; lc.ref = f.leaf_refs[i]; lc.mesh = -1;
+                for (int k = 0; k < 6; k++) lc.box[k] = f.leaf_box[6 * i + k];
+                int enc = ~lc.ref, kind = enc & 7, idx = enc >> RTB_KIND_BITS;
+                if (kind != KIND_SPHERE)
+                    for (int t = 0; t < 3 * (kind == KIND_TRI ? 1 : 2); t++) lc.rec[t] = f.tris[3 * (size_t)idx + t];
+                cands.push_back(lc);
+            }
+        for (size_t mi = 0; mi < f.dev_meshes.size(); mi++) {
+            const DevMesh &m = f.dev_meshes[mi];
+            if (m.prep.kept <= 0) continue;
+            int2 *d_list = (int2 *)(d_scratch + 8);
+            RTB_CUDA(c, cudaMemsetAsync(d_scratch + 6, 0, sizeof(int), c->stream), "large primitives of the mesh");
+            RTB_CUDA(c, mesh_large_candidates(w_tris, (int)m.tri_base, m.prep.kept, threshold, d_scratch + 6, d_list, CAND_CAP, c->stream), "large primitives of the mesh");
+            int count = 0;
+            std::vector<int2> list(CAND_CAP);
+            RTB_CUDA(c, cudaMemcpyAsync(&count, d_scratch + 6, sizeof(int), cudaMemcpyDeviceToHost, c->stream), "large primitives of the mesh");
+            RTB_CUDA(c, cudaMemcpyAsync(list.data(), d_list, sizeof(int2) * CAND_CAP, cudaMemcpyDeviceToHost, c->stream), "large primitives of the mesh");
+            RTB_CUDA(c, cudaStreamSynchronize(c->stream), "large primitives of the mesh");
+            for (int q = 0; q < std::min(count, CAND_CAP); q++) {
+                LargeCand lc{};
+                std::memcpy(&lc.area, &list[q].y, sizeof(float));
+                lc.order = (long long)m.leaf_base + list[q].x;
+                lc.ref = ~(((int)(m.tri_base + list[q].x) << RTB_KIND_BITS) | KIND_TRI);
+                lc.mesh = (int)mi;
+                cands.push_back(lc);
+            }
         }
-    } else {
-        small = f.leaf_refs;
-        for (size_t i = 0; i < f.leaf_refs.size(); i++) small_idx.push_back((int)i);
+        std::sort(cands.begin(), cands.end(), [](const LargeCand &x, const LargeCand &y) { return x.area != y.area ? x.area > y.area : x.order < y.order; });
+        size_t limit = (size_t)std::max(0, std::min(c->opt_max_large, 32));  // bit masks of 32
+        if (cands.size() > limit) cands.resize(limit);
+        std::sort(cands.begin(), cands.end(), [](const LargeCand &x, const LargeCand &y) { return x.order < y.order; });
+        for (LargeCand &lc : cands)
+            if (lc.mesh >= 0) {  // a triangle of a device mesh: fetch its record
+                int idx = (~lc.ref) >> RTB_KIND_BITS;
+                RTB_CUDA(c, cudaMemcpyAsync(lc.rec, w_tris + 3 * (size_t)idx, 3 * sizeof(float4), cudaMemcpyDeviceToHost, c->stream), "large primitives of the mesh");
+                RTB_CUDA(c, cudaStreamSynchronize(c->stream), "large primitives of the mesh");
+                rec_box(lc.rec, 1, lc.box, lc.box + 3);
+            }
     }
-    const int *d_small = nullptr;
+    std::vector<int> large, small, small_idx;  // small_idx: position of each (host-built) tree primitive in f.leaf_refs / f.leaf_box
+    {
+        std::vector<char> is_large(host_leaves, 0);
+        for (const LargeCand &lc : cands) {
+            large.push_back(lc.ref);
+            if (lc.mesh < 0) is_large[(size_t)lc.order] = 1;
+        }
+        for (size_t i = 0; i < host_leaves; i++)
+            if (!is_large[i]) { small.push_back(f.leaf_refs[i]); small_idx.push_back((int)i); }
+    }
     // padded boxes of the large primitives (conservative pre-test before the exact one)
     std::vector<float4> large_boxes;
-    {
-        std::vector<int> pos(f.leaf_refs.size());
-        size_t li = 0;
-        for (size_t i = 0; i < f.leaf_refs.size() && li < large.size(); i++) {
-            if (f.leaf_refs[i] != large[li]) continue;
-            const float *b = &f.leaf_box[6 * i];
-            float lo[3], hi[3];
-            for (int k = 0; k < 3; k++) {
-                float pad = 4e-7f * fmaxf(fmaxf(fabsf(b[k]), fabsf(b[3 + k])), b[3 + k] - b[k]) + 1e-12f;
-                lo[k] = b[k] - pad; hi[k] = b[3 + k] + pad;
-            }
-            // A primitive that is flat on a coordinate axis (walls, floors: every side vector has an exactly zero
-            // component there) gets that axis + 1 in lo.w: large_prims_best then proves, from the slab of that axis
-            // alone, that Triangle::hit would return a distance below its 1e-6 threshold (the ray STARTS on this
-            // wall) and skips the two exact tests.  See the derivation there.
-            int flat_axis = 0;
-            {
-                int enc = ~large[li], kind = enc & 7, idx = enc >> RTB_KIND_BITS;
-                if (kind != KIND_SPHERE) {
-                    int count = kind == KIND_TRI ? 1 : 2;
-                    bool flat[3] = {true, true, true};
-                    for (int t = 0; t < count; t++) {
-                        float4 ta = f.tris[3 * (size_t)(idx + t)], tb = f.tris[3 * (size_t)(idx + t) + 1], tc = f.tris[3 * (size_t)(idx + t) + 2];
-                        float s1[3] = {ta.w, tb.x, tb.y}, s2[3] = {tb.z, tb.w, tc.x};
-                        for (int k2 = 0; k2 < 3; k2++) flat[k2] = flat[k2] && s1[k2] == 0.f && s2[k2] == 0.f;
-                        if (t == 1) {  // both triangles of a quad start at the same point (Quad::create_triangles, objects.cu:244-253)
-                            float4 t0 = f.tris[3 * (size_t)idx];
-                            if (t0.x != ta.x || t0.y != ta.y || t0.z != ta.z) flat[0] = flat[1] = flat[2] = false;
-                        }
-                    }
-                    for (int k2 = 0; k2 < 3; k2++)
-                        if (flat[k2] && flat_axis == 0) flat_axis = k2 + 1;
+    for (const LargeCand &lc : cands) {
+        const float *b = lc.box;
+        float lo[3], hi[3];
+        for (int k = 0; k < 3; k++) {
+            float pad = 4e-7f * fmaxf(fmaxf(fabsf(b[k]), fabsf(b[3 + k])), b[3 + k] - b[k]) + 1e-12f;
+            lo[k] = b[k] - pad; hi[k] = b[3 + k] + pad;
+        }
+        // A primitive that is flat on a coordinate axis (walls, floors: every side vector has an exactly zero
+        // component there) gets that axis + 1 in lo.w: large_prims_best then proves, from the slab of that axis
+        // alone, that Triangle::hit would return a distance below its 1e-6 threshold (the ray STARTS on this
+        // wall) and skips the two exact tests.  See the derivation there.
+        int flat_axis = 0;
+        int kind = (~lc.ref) & 7;
+        if (kind != KIND_SPHERE) {
+            int count = kind == KIND_TRI ? 1 : 2;
+            bool flat[3] = {true, true, true};
+            for (int t = 0; t < count; t++) {
+                float4 ta = lc.rec[3 * t], tb = lc.rec[3 * t + 1], tc = lc.rec[3 * t + 2];
+                float s1[3] = {ta.w, tb.x, tb.y}, s2[3] = {tb.z, tb.w, tc.x};
+                for (int k2 = 0; k2 < 3; k2++) flat[k2] = flat[k2] && s1[k2] == 0.f && s2[k2] == 0.f;
+                if (t == 1) {  // both triangles of a quad start at the same point (Quad::create_triangles, objects.cu:244-253)
+                    float4 t0 = lc.rec[0];
+                    if (t0.x != ta.x || t0.y != ta.y || t0.z != ta.z) flat[0] = flat[1] = flat[2] = false;
                 }
             }
-            float4 lo4 = make_float4(lo[0], lo[1], lo[2], 0.f);
-            std::memcpy(&lo4.w, &flat_axis, sizeof(int));
-            large_boxes.push_back(lo4);
-            large_boxes.push_back(make_float4(hi[0], hi[1], hi[2], 0.f));
-            li++;
+            for (int k2 = 0; k2 < 3; k2++)
+                if (flat[k2] && flat_axis == 0) flat_axis = k2 + 1;
         }
+        float4 lo4 = make_float4(lo[0], lo[1], lo[2], 0.f);
+        std::memcpy(&lo4.w, &flat_axis, sizeof(int));
+        large_boxes.push_back(lo4);
+        large_boxes.push_back(make_float4(hi[0], hi[1], hi[2], 0.f));
     }
     RTB_CUDA(c, upload(c, large_boxes, &d.large_boxes), "uploading large-primitive boxes");
     for (size_t i = 0; i < 2 * RTB_MAX_LARGE; i++) d.large_box_c[i] = i < large_boxes.size() ? large_boxes[i] : make_float4(0, 0, 0, 0);
     RTB_CUDA(c, upload(c, large, &d.large_refs), "uploading large-primitive list");
-    RTB_CUDA(c, upload(c, small, &d_small), "uploading tree primitive list");
+    // the tree's primitive list: the host-built leaves that are not large, then the device meshes' (a large one is
+    // replaced by the last of its mesh: the order of the list does not matter to the builder)
+    size_t dev_large = 0;
+    for (const LargeCand &lc : cands) dev_large += lc.mesh >= 0;
+    const size_t small_total = small.size() + dev_kept - dev_large;
+    int *w_small = nullptr;
+    RTB_CUDA(c, upload_front(c, small, small.size() + dev_kept, &w_small), "uploading tree primitive list");  // room for every mesh's whole list: the large ones leave after the copy
+    {
+        size_t cursor = small.size();
+        for (size_t mi = 0; mi < f.dev_meshes.size(); mi++) {
+            const DevMesh &m = f.dev_meshes[mi];
+            size_t span = (size_t)m.prep.kept;
+            if (span == 0) continue;
+            {
+                cudaError_t ce = cudaMemcpyAsync(w_small + cursor, w_all_refs + m.leaf_base, sizeof(int) * span, cudaMemcpyDeviceToDevice, c->stream);
+                if (ce != cudaSuccess) {
+                    char msg[256];
+                    std::snprintf(msg, sizeof msg, "%s (mesh %zu: span %zu at %zu of %zu, from %zu of %zu; last error %s)", cudaGetErrorString(ce), mi, span, cursor, small_total,
+                                  m.leaf_base, total_leaves, cudaGetErrorString(cudaPeekAtLastError()));
+                    return fail(c, "copying the mesh's primitive list", msg);
+                }
+            }
+            std::vector<size_t> removed;
+            for (const LargeCand &lc : cands)
+                if (lc.mesh == (int)mi) removed.push_back((size_t)(lc.order - (long long)m.leaf_base));
+            std::sort(removed.rbegin(), removed.rend());
+            for (size_t pos : removed) {  // descending: the tail never holds a removed entry
+                if (pos != span - 1)
+                    RTB_CUDA(c, cudaMemcpyAsync(w_small + cursor + pos, w_small + cursor + span - 1, sizeof(int), cudaMemcpyDeviceToDevice, c->stream), "filling the gap of a large primitive in the mesh's list");
+                span--;
+            }
+            cursor += span;
+        }
+    }
+    const int *d_small = w_small;
     d.num_large = (int)large.size();
     d.large_sphere_mask = 0;
     for (size_t i = 0; i < large.size() && i < 32; i++)
         if (((~large[i]) & 7) == KIND_SPHERE) d.large_sphere_mask |= 1u << i;
-    d.num_bvh_prims = (int)small.size();
-    d.num_tris = (int)f.tri_ids.size();
+    d.num_bvh_prims = (int)small_total;
+    d.num_tris = (int)total_tris;
     d.num_spheres = (int)f.sphere_ids.size();
     d.num_objects = (int)c->objects.size();
     c->culled_tris = f.culled;
@@ -1578,6 +1778,61 @@ int rtb_primary_ids(rtb_ctx *c, int32_t *obj_id, int32_t *sub_id, float *t) {
     return 0;
 }
 
+// Test hook: the reference-BVH partition of one mesh by the host restatement (rtb_refbvh.cpp) or by the device version
+// (rtb_meshprep.cu), so that a test can compare the two array by array.
+int rtb_debug_mesh_partition(int device, const float *tri_points, int n, int on_device, int32_t *leaf_of, uint8_t *degenerate, float *nodes,
+                             int nodes_cap, int *num_nodes) {
+    if (!tri_points || n <= 0 || !leaf_of || !degenerate || !nodes || !num_nodes) return 1;
+    if (!on_device) {
+        RefBvh rb;
+        ref_bvh_partition(tri_points, n, rb);
+        *num_nodes = (int)rb.nodes.size();
+        if (*num_nodes > nodes_cap) return 1;
+        for (int i = 0; i < n; i++) { leaf_of[i] = rb.leaf_of[i]; degenerate[i] = (uint8_t)rb.degenerate[i]; }
+        for (int q = 0; q < *num_nodes; q++) {
+            const RefBvhNode &nd = rb.nodes[q];
+            float *o = nodes + 8 * (size_t)q;
+            o[0] = nd.lo[0]; o[1] = nd.lo[1]; o[2] = nd.lo[2]; o[3] = (float)nd.parent;
+            o[4] = nd.hi[0]; o[5] = nd.hi[1]; o[6] = nd.hi[2]; o[7] = 0.f;
+        }
+        return 0;
+    }
+    int prev = -1;
+    cudaGetDevice(&prev);
+    if (cudaSetDevice(device) != cudaSuccess) return 1;
+    float *d_pts = nullptr;
+    MeshPrep prep;
+    int nonfinite = 0, rc = 1;
+    std::vector<int> slot((size_t)n);
+    cudaError_t e = cudaMalloc((void **)&d_pts, sizeof(float) * 9 * (size_t)n);
+    if (e == cudaSuccess) e = cudaMemcpy(d_pts, tri_points, sizeof(float) * 9 * (size_t)n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = mesh_partition_device(d_pts, n, nullptr, prep, &nonfinite);
+    if (e == cudaSuccess) e = cudaMemcpy(leaf_of, prep.d_leaf_of, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(slot.data(), prep.d_slot, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && !nonfinite && (int)(prep.nodes.size() / 2) <= nodes_cap) {
+        *num_nodes = (int)(prep.nodes.size() / 2);
+        int kept = 0;
+        bool ordered = true;
+        for (int i = 0; i < n; i++) {
+            degenerate[i] = slot[i] < 0;
+            if (slot[i] >= 0) ordered = ordered && slot[i] == kept++;
+        }
+        for (int q = 0; q < *num_nodes; q++) {
+            float4 lo = prep.nodes[2 * (size_t)q], hi = prep.nodes[2 * (size_t)q + 1];
+            int parent;
+            std::memcpy(&parent, &lo.w, sizeof(int));
+            float *o = nodes + 8 * (size_t)q;
+            o[0] = lo.x; o[1] = lo.y; o[2] = lo.z; o[3] = (float)parent;
+            o[4] = hi.x; o[5] = hi.y; o[6] = hi.z; o[7] = 0.f;
+        }
+        rc = (ordered && kept == prep.kept) ? 0 : 1;
+    }
+    cudaFree(d_pts);
+    prep.release();
+    if (prev >= 0) cudaSetDevice(prev);
+    return rc;
+}
+
 int rtb_counters(rtb_ctx *c, RtbCounters *out) {
     if (!c || !out) return 1;
     *out = c->last_counters;
@@ -1603,6 +1858,10 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "stream_shade_sms") { c->opt_stream_shade_sms = value; c->stream_shade_sms = 0; }
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
     else if (k == "builder") c->opt_builder = value;
+    else if (k == "device_flatten") {   // takes effect at the next commit
+        if (value < 0 || value > 2) return fail(c, "rtb_set_option", "device_flatten: 0 = meshes flattened on the host, 1 = on the device, 2 = on the device from 32768 triangles up");
+        c->opt_device_flatten = value;
+    }
     else if (k == "ploc_radius") c->opt_ploc_radius = value;
     else if (k == "large_split") c->opt_large_split = value;          // takes effect at the next commit
     else if (k == "max_large") c->opt_max_large = value;
@@ -1665,6 +1924,9 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "comm_world") *value = c->comm ? c->comm_world : 1;
     else if (k == "build_ms") *value = c->build_ms;
     else if (k == "commit_ms") *value = c->commit_ms;
+    else if (k == "commit_partition_ms") *value = c->commit_partition_ms;
+    else if (k == "commit_flatten_ms") *value = c->commit_flatten_ms;
+    else if (k == "commit_upload_ms") *value = c->commit_upload_ms;
     else if (k == "kernel") *value = effective_kernel(c);      // the variant frames are rendered with
     else if (k == "kernel_option") *value = c->opt_kernel;     // 0, 1 or 2 = auto
     else if (k == "kernel_tuned") *value = c->opt_kernel == 2 && c->auto_choice >= 0 ? 1 : 0;
@@ -1681,6 +1943,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "wf_shade_ms") *value = c->wf_shade_ms;
     else if (k == "wf_traverse_ms") *value = c->wf_traverse_ms;
     else if (k == "wf_total_ms") *value = c->wf_total_ms;
+    else if (k == "device_flatten") *value = c->opt_device_flatten;
     else if (k == "builder") *value = c->opt_builder;
     else if (k == "launches_per_frame") {  // kernels of ONE frame: megakernel 1; wavefront per row group 1 + 2 * spp * bounces + 3 per queue rebuild
         double it = (double)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);

@@ -30,11 +30,14 @@ struct rtb_ctx {
     std::vector<std::vector<float>> image_data;
     std::vector<RtbImage> images;
     bool committed = false;
+    bool mesh_uv_given = false;      // some mesh came with texture points (else the device flatten writes zeros instead of uploading them)
+    int opt_device_flatten = 2;      // meshes partitioned + flattened on the device: 0 never, 1 always, 2 = from 32768 triangles up
 
     // device scene
     DScene d{};
     std::vector<void *> scene_allocs;
     double build_ms = 0, commit_ms = 0;  // device time of the tree build / wall time of the whole commit
+    double commit_partition_ms = 0, commit_flatten_ms = 0, commit_upload_ms = 0;  // wall-time parts of the last commit: reference-BVH partition (inside the flatten), whole flatten, uploads
     size_t scene_bytes = 0;
     int culled_tris = 0, tree_height = 0;
 

@@ -158,6 +158,22 @@ __device__ __forceinline__ bool box_test(float4 lo, float4 hi, const Ray &r, flo
     return tmin <= tmax * 1.000004f;
 }
 
+// box_test against [0, inf) that also hands out, per axis, the larger of the two slab distances (what the flat-wall
+// skip of large_prims_best needs: the same products, not recomputed)
+__device__ __forceinline__ bool box_test_far(float4 lo, float4 hi, const Ray &r, float &fx, float &fy, float &fz) {
+    float t1 = (lo.x - r.o.x) * r.inv.x, t2 = (hi.x - r.o.x) * r.inv.x;
+    float tmin = fminf(t1, t2), tmax = fx = fmaxf(t1, t2);
+    t1 = (lo.y - r.o.y) * r.inv.y; t2 = (hi.y - r.o.y) * r.inv.y;
+    fy = fmaxf(t1, t2);
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fy);
+    t1 = (lo.z - r.o.z) * r.inv.z; t2 = (hi.z - r.o.z) * r.inv.z;
+    fz = fmaxf(t1, t2);
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fz);
+    tmin = fmaxf(tmin, 0.f);
+    tmax = fminf(tmax, RTB_INF_F);
+    return tmin <= tmax * 1.000004f;
+}
+
 #define RTB_DONE 0x7fffffff
 
 // Resumable traversal state of one ray: lives in the lane across iterations of the megakernel's
@@ -185,23 +201,22 @@ __device__ __forceinline__ void large_prims_best(const DScene &s, const Ray &r, 
     best.t = RTB_INF_F; best.u = 0; best.v = 0; best.code = -1;
     unsigned cand = 0;
     for (int i = 0; i < s.num_large; i++) {
-        float tn;
         RTB_COUNT(cnt, box);
         const float4 lo = s.large_box_c[2 * i], hi = s.large_box_c[2 * i + 1];
-        bool c = box_test(lo, hi, r, RTB_INF_F, tn);
+        float fx, fy, fz;
+        bool c = box_test_far(lo, hi, r, fx, fy, fz);
         // A ray that STARTS on a wall meets that wall's box at t ~ 0, and Triangle::hit (objects.cu:135-163) then
         // runs twice only to fail `dist > 1e-6`.  For a primitive that is flat on axis k (every side vector has an
         // exactly zero k component, checked at commit) the products of Triangle::hit that multiply those zeros vanish
         // exactly, and what remains is dist = -(o_k - p0_k) / d_k up to the rounding of a 2-D cross product that is
         // formed the same way in numerator and denominator (relative error a few 1e-7 / sin(angle between the sides)).
         // o_k - p0_k is exact (Sterbenz) and lies inside the padded slab, so max((lo_k - o_k) / d_k, (hi_k - o_k) / d_k)
-        // bounds dist from above: below 0.99e-6 the reference's test rejects both triangles, whatever u and v say.
-        // NaN / inf (d_k == 0) compare false and take the exact tests.
+        // -- the far slab distance of axis k, which the box test has just formed -- bounds dist from above: below
+        // 0.99e-6 the reference's test rejects both triangles, whatever u and v say.
+        // NaN / inf (d_k == 0) compare false and take the exact tests.  flat_axis is uniform (kernel parameter).
         int flat_axis = __float_as_int(lo.w);
         if (flat_axis) {
-            float lk = flat_axis == 1 ? lo.x : (flat_axis == 2 ? lo.y : lo.z), hk = flat_axis == 1 ? hi.x : (flat_axis == 2 ? hi.y : hi.z);
-            float ok = flat_axis == 1 ? r.o.x : (flat_axis == 2 ? r.o.y : r.o.z), ik = flat_axis == 1 ? r.inv.x : (flat_axis == 2 ? r.inv.y : r.inv.z);
-            float tk = fmaxf((lk - ok) * ik, (hk - ok) * ik);
+            float tk = flat_axis == 1 ? fx : (flat_axis == 2 ? fy : fz);
             if (tk < 0.99e-6f) c = false;
         }
         if (c) cand |= 1u << i;
