@@ -9,9 +9,10 @@ run() {
   if [ "$N" = "1" ]; then python bench.py --gpus 1 "$@"
   else python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@"; fi
 }
-for W in C3 C1 C2 C4 C5; do
+WL="C3 C1 C2 C4 C5"; [ "$N" != "1" ] && WL="C3 C1 C2 C5"   # C4 tile-sharded rides along with C3 as c4_tiles
+for W in $WL; do
   extra="--no-c4-tiles"; [ "$W" = "C3" ] && extra=""
-  run --workload $W --steps 5 --warmup 3 --no-cpu-baseline $extra 2> $O/r2_bench_${W}_n${N}.err | grep "^{" > $O/r2_bench_${W}_n${N}.json
+  run --workload $W --steps 4 --warmup 3 --no-cpu-baseline $extra 2> $O/r2_bench_${W}_n${N}.err | grep "^{" > $O/r2_bench_${W}_n${N}.json
   echo "$W rc=${PIPESTATUS[0]}"
   python - <<PY
 import json
