@@ -809,10 +809,10 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
         RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_state, slots * 6 * sizeof(float4)), "allocating wavefront state");
         RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_queue, slots * 3 * sizeof(int)), "allocating wavefront queues");
         RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_alive, slots), "allocating wavefront flags");
-        RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_block_count, 2 * ((slots + 255) / 256 + 2) * sizeof(int)), "allocating wavefront scan buffers");
+        RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_block_count, RTB_WF_MAX_LANES * ((slots + 255) / 256 + 2) * sizeof(int)), "allocating wavefront scan buffers");
         c->wf_slots = slots;
     }
-    if (!c->d_wf_counts) RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_counts, 16 * sizeof(unsigned int)), "allocating wavefront counters");
+    if (!c->d_wf_counts) RTB_CUDA(c, cudaMalloc((void **)&c->d_wf_counts, 8 * RTB_WF_MAX_LANES * sizeof(unsigned int)), "allocating wavefront counters");
     if (c->wf_shade_per_sm == 0) {
         cudaError_t e = c->opt_strict ? strict::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm) : fast::wf_occupancy(&c->wf_shade_per_sm, &c->wf_trav_per_sm);
         if (e != cudaSuccess || c->wf_shade_per_sm <= 0 || c->wf_trav_per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
@@ -843,7 +843,6 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     base.counters = c->opt_counters ? c->d_counters : nullptr;
     const bool brute = c->opt_traversal == 1, count_ops = c->opt_counters != 0, strict_fp = c->opt_strict != 0;
     int trav_per_sm = c->opt_blocks_per_sm > 0 ? std::min(c->opt_blocks_per_sm, c->wf_trav_per_sm) : c->wf_trav_per_sm;
-    const int trav_blocks = c->num_sms * trav_per_sm;
     const long long iterations = (long long)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
     const long long rebuild_every = c->opt_wf_rebuild;
     constexpr int WF_PACE_STEP = 8, WF_PACE_RING = 64;
@@ -853,16 +852,25 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     // iterations before the next (a group's records then stay L2-resident), two groups at a time on
     // two streams (the launch gaps and the tails of one group's kernels are filled by the other's).
     int groups = std::max(1, std::min(c->opt_wf_groups, local_rows));
-    const int lanes = (c->opt_wf_streams >= 2 && groups >= 2) ? 2 : 1;
-    if (lanes == 2 && !c->stream2) {
-        RTB_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "creating the second stream");
-        RTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming), "creating events");
-        RTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming), "creating events");
+    // `lanes` row groups are in flight at once, each on its own stream with its own queues and counters: a group's
+    // launch gaps, ramps and tails -- and the longest ray of its iteration -- are filled by the other groups' kernels.
+    // Beyond two lanes every group's traversal grid shrinks, so that the groups' persistent blocks fit side by side.
+    const int lanes = std::max(1, std::min(std::min(c->opt_wf_streams, groups), RTB_WF_MAX_LANES));
+    if (lanes > 2 && c->opt_blocks_per_sm <= 0) trav_per_sm = std::max(1, 2 * trav_per_sm / lanes);
+    const int trav_blocks = c->num_sms * trav_per_sm;
+    cudaStream_t streams[RTB_WF_MAX_LANES];
+    streams[0] = c->stream;
+    for (int l = 1; l < lanes; l++) {
+        if (!c->lane_stream[l]) {
+            RTB_CUDA(c, cudaStreamCreateWithFlags(&c->lane_stream[l], cudaStreamNonBlocking), "creating a render stream");
+            RTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join[l], cudaEventDisableTiming), "creating events");
+        }
+        streams[l] = c->lane_stream[l];
     }
-    cudaStream_t streams[2] = {c->stream, lanes == 2 ? c->stream2 : c->stream};
-    if (lanes == 2) {
+    if (lanes > 1) {
+        if (!c->ev_fork) RTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming), "creating events");
         RTB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream), "forking the render streams");
-        RTB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0), "forking the render streams");
+        for (int l = 1; l < lanes; l++) RTB_CUDA(c, cudaStreamWaitEvent(streams[l], c->ev_fork, 0), "forking the render streams");
     }
     const bool timing = c->opt_wf_timing != 0 && groups == 1;
     c->wf_events_used = 0;
@@ -896,7 +904,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
     cudaError_t e = cudaSuccess;
     const int rows_per_group = (local_rows + groups - 1) / groups;
     for (int g0 = 0; g0 < groups && e == cudaSuccess; g0 += lanes) {
-        Group gr[2];
+        Group gr[RTB_WF_MAX_LANES];
         int active = 0;
         for (int l = 0; l < lanes && g0 + l < groups; l++) {
             Group &g = gr[active];
@@ -952,9 +960,9 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
             }
         }
     }
-    if (lanes == 2 && e == cudaSuccess) {
-        e = cudaEventRecord(c->ev_join, c->stream2);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, c->ev_join, 0);
+    for (int l = 1; l < lanes && e == cudaSuccess; l++) {
+        e = cudaEventRecord(c->ev_join[l], streams[l]);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, c->ev_join[l], 0);
     }
     if (e != cudaSuccess) return fail(c, "launching wavefront kernels", cudaGetErrorString(e));
     if (timing) {  // events: [start] shade0 [1] {traverse [2k+2] shade [2k+3]}
@@ -1100,8 +1108,10 @@ void rtb_destroy(rtb_ctx *c) {
     if (c->d_tune_scratch) cudaFree(c->d_tune_scratch);
     for (cudaEvent_t ev : c->wf_events) cudaEventDestroy(ev);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->ev_join) cudaEventDestroy(c->ev_join);
-    if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
+    for (int l = 1; l < RTB_WF_MAX_LANES; l++) {
+        if (c->ev_join[l]) cudaEventDestroy(c->ev_join[l]);
+        if (c->lane_stream[l]) { cudaStreamSynchronize(c->lane_stream[l]); cudaStreamDestroy(c->lane_stream[l]); }
+    }
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);

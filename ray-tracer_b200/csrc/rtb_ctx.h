@@ -11,6 +11,8 @@ using namespace rtb;
 
 std::string &rtb_create_error();  // message of a failed rtb_create (no context yet)
 
+#define RTB_WF_MAX_LANES 8   // row groups of the wavefront kernels in flight at once, each on its own stream
+
 struct rtb_ctx {
     int device = 0;
     int num_sms = 0;
@@ -55,7 +57,7 @@ struct rtb_ctx {
     cudaEvent_t frame_done[4] = {nullptr, nullptr, nullptr, nullptr};  // end of the last frames (bounded run-ahead)
     long long frames_enqueued = 0;
     int opt_run_ahead = 0;
-    cudaEvent_t pace_events[2][64] = {};   // wavefront loop: per stream, one event every 8 iterations (bounded run-ahead)
+    cudaEvent_t pace_events[RTB_WF_MAX_LANES][64] = {};   // wavefront loop: per stream, one event every 8 iterations (bounded run-ahead)
     int opt_wf_pace = 0;
 
     // wavefront variant: per-pixel records, two queues, counters {n[0], n[1], fetch}
@@ -70,8 +72,8 @@ struct rtb_ctx {
     int opt_wf_timing = 0;
     int opt_wf_rebuild = 16;  // iterations between queue rebuilds (0 = never)
     int opt_wf_groups = 2, opt_wf_streams = 2;  // row groups taken through the frame one after the other / concurrent groups
-    cudaStream_t stream2 = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t lane_stream[RTB_WF_MAX_LANES] = {};   // [0] unused (lane 0 runs on `stream`); created at first use
+    cudaEvent_t ev_fork = nullptr, ev_join[RTB_WF_MAX_LANES] = {};
     std::vector<cudaEvent_t> wf_events;
     size_t wf_events_used = 0;
     double wf_shade_ms = 0, wf_traverse_ms = 0, wf_total_ms = 0;

@@ -133,9 +133,10 @@ def test_wavefront_equals_megakernel(tracer, sid, p0, p1):
             assert out[0][2][k] == other[2][k]
 
 
-@pytest.mark.parametrize("groups,streams", [(2, 1), (3, 2), (7, 2)])
+@pytest.mark.parametrize("groups,streams", [(2, 1), (3, 2), (7, 2), (4, 4), (8, 8), (11, 5), (40, 16)])
 def test_wavefront_row_groups_and_streams(tracer, groups, streams):
-    """Row groups (L2 residency) and two concurrent streams only reorder the work: same bits."""
+    """Row groups (L2 residency) and up to eight of them in flight on their own streams only reorder the work: same
+    bits (more streams than the library has lanes, or than there are groups, are clamped)."""
     scene = _scene(0, 0, 0)
     Ws, Hs = 203, 151
     tracer.setup(scene, Ws, Hs, 3, 4)
