@@ -432,7 +432,8 @@ class Job:
         tuned = (f"auto: {KERNEL_DESC[kind].split(':')[0]} kept after timing the variants on a {min(self.spp, 8)}-spp frame "
                  f"(wavefront {tr.info('tune_wavefront_ms'):.2f} ms, megakernel {tr.info('tune_megakernel_ms'):.2f} ms)"
                  if int(tr.info("kernel_tuned")) else "fixed by --kernel")
-        policy = f", traversal policy walk_min {int(tr.info('walk_min'))} / refill {int(tr.info('wf_refill'))}" if kind != 0 else f", walk_min {int(tr.info('walk_min'))}"
+        policy = (f", traversal policy walk_min {int(tr.info('walk_min'))} / refill {int(tr.info('wf_refill'))}" if kind != 0 else
+                  f", walk_min {int(tr.info('walk_min'))}" + (", stack entries fetched with the node (early-pop variant)" if int(tr.info("mega_early_pop")) else ""))
         return kind, KERNEL_DESC[kind] + (", PLOC tree" if int(tr.info("builder")) == 1 else ", Karras LBVH") + policy, tuned
 
     def close(self):

@@ -530,13 +530,17 @@ int autotune_kernel(rtb_ctx *c) {
     if (c->opt_tune_set & 16) { cand.push_back({4, 16, 8, 0.f}); cand.push_back({4, 12, 16, 0.f}); }
     if (c->opt_tune_set & 8) { cand.push_back({3, 16, 8, 0.f}); cand.push_back({3, 12, 16, 0.f}); }
     if (c->opt_tune_set & 2) { cand.push_back({1, 16, 8, 0.f}); cand.push_back({1, 12, 16, 0.f}); }
-    if (c->opt_tune_set & 1) cand.push_back({0, 0, 0, 0.f});
+    if (c->opt_tune_set & 1) {   // megakernel: `refill` = its early-pop variant (both, unless option "mega_early_pop" pins one)
+        if (c->opt_mega_early_pop != 1) cand.push_back({0, 0, 0, 0.f});
+        if (c->opt_mega_early_pop != 0) cand.push_back({0, 0, 1, 0.f});
+    }
     const bool pinned = c->opt_walk_min > 0 && c->opt_wf_refill > 0;  // both knobs pinned by the caller: one policy per kernel
     int warmed = 0;  // kernels whose first (1-spp) frame has run
     for (size_t i = 0; i < cand.size() && rc == 0; i++) {
         const bool second_policy = i > 0 && cand[i - 1].kern == cand[i].kern;
-        if (second_policy && pinned) { cand[i].ms = 1e30f; continue; }
-        c->tuned_walk_min = cand[i].walk_min; c->tuned_refill = cand[i].refill;
+        if (second_policy && pinned && cand[i].kern != 0) { cand[i].ms = 1e30f; continue; }
+        if (cand[i].kern == 0) c->tuned_mega_early_pop = cand[i].refill;
+        else { c->tuned_walk_min = cand[i].walk_min; c->tuned_refill = cand[i].refill; }
         // pass plan: a 1-spp frame warms a kernel up the first time it runs, then the timed frame.  The streaming
         // kernel balances its SM split from the utilisation the previous frame measured: two more short frames
         // let it settle before the timed one.
@@ -571,7 +575,14 @@ int autotune_kernel(rtb_ctx *c) {
         if (slot == 0 || cand[i].ms < slot) slot = cand[i].ms;
     }
     c->auto_choice = cand[best].kern;
-    c->tuned_walk_min = cand[best].walk_min; c->tuned_refill = cand[best].refill;
+    // the megakernel keeps its better variant even when another kernel wins (pinning kernel = 0 later uses it)
+    {
+        float best_mega = 1e30f;
+        for (const Cand &cd : cand)
+            if (cd.kern == 0 && cd.ms > 0 && cd.ms < best_mega) { best_mega = cd.ms; c->tuned_mega_early_pop = cd.refill; }
+    }
+    if (cand[best].kern != 0) { c->tuned_walk_min = cand[best].walk_min; c->tuned_refill = cand[best].refill; }
+    else { c->tuned_walk_min = 16; c->tuned_refill = 8; }
     return 0;
 }
 
@@ -753,6 +764,8 @@ int launch_frame_pool(rtb_ctx *c, int time_ms, int frame_num) {
 }
 
 int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num) {
+    // the traversal-loop variant (trav_run, EARLY_POP): pinned by option "mega_early_pop", else what the timed choice kept
+    const bool early_pop = c->opt_mega_early_pop >= 0 ? c->opt_mega_early_pop != 0 : c->tuned_mega_early_pop != 0;
     RenderParams p;
     p.scene = c->d;
     std::memcpy(&p.cam, &c->cam, sizeof(DCamera));
@@ -780,12 +793,12 @@ int launch_frame_megakernel(rtb_ctx *c, int time_ms, int frame_num) {
     cfg.threads = c->opt_threads;
     int per_sm = c->opt_blocks_per_sm;
     if (per_sm <= 0) {
-        cudaError_t e = c->opt_strict ? strict::render_occupancy(cfg.threads, &per_sm) : fast::render_occupancy(cfg.threads, &per_sm);
+        cudaError_t e = c->opt_strict ? strict::render_occupancy(cfg.threads, early_pop, &per_sm) : fast::render_occupancy(cfg.threads, early_pop, &per_sm);
         if (e != cudaSuccess || per_sm <= 0) return fail(c, "querying occupancy", cudaGetErrorString(e));
     }
     cfg.blocks = c->num_sms * per_sm;
-    cudaError_t e = c->opt_strict ? strict::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream)
-                                  : fast::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, cfg, c->stream);
+    cudaError_t e = c->opt_strict ? strict::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, early_pop, cfg, c->stream)
+                                  : fast::launch_render(p, c->opt_traversal == 1, c->opt_counters != 0, early_pop, cfg, c->stream);
     if (e != cudaSuccess) return fail(c, "launching render kernel", cudaGetErrorString(e));
     return 0;
 }
@@ -1867,6 +1880,7 @@ int rtb_set_option(rtb_ctx *c, const char *key, int value) {
     else if (k == "stream_slots") c->opt_stream_slots = value < 1 ? 1 : value;
     else if (k == "stream_shade_sms") { c->opt_stream_shade_sms = value; c->stream_shade_sms = 0; }
     else if (k == "reference_bvh_quirks") c->opt_ref_quirks = value;  // takes effect at the next commit
+    else if (k == "mega_early_pop") c->opt_mega_early_pop = value < 0 ? -1 : (value != 0);   // megakernel traversal variant: -1 = timed choice
     else if (k == "builder") c->opt_builder = value;
     else if (k == "device_flatten") {   // takes effect at the next commit
         if (value < 0 || value > 2) return fail(c, "rtb_set_option", "device_flatten: 0 = meshes flattened on the host, 1 = on the device, 2 = on the device from 32768 triangles up");
@@ -1954,6 +1968,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "wf_traverse_ms") *value = c->wf_traverse_ms;
     else if (k == "wf_total_ms") *value = c->wf_total_ms;
     else if (k == "device_flatten") *value = c->opt_device_flatten;
+    else if (k == "mega_early_pop") *value = c->opt_mega_early_pop >= 0 ? c->opt_mega_early_pop : c->tuned_mega_early_pop;
     else if (k == "builder") *value = c->opt_builder;
     else if (k == "launches_per_frame") {  // kernels of ONE frame: megakernel 1; wavefront per row group 1 + 2 * spp * bounces + 3 per queue rebuild
         double it = (double)std::max(0, c->rd.rays_per_pixel) * std::max(0, c->rd.reflection_limit);
@@ -1968,7 +1983,7 @@ int rtb_get_info(rtb_ctx *c, const char *key, double *value) {
     else if (k == "block_threads") *value = c->opt_threads;
     else if (k == "blocks_per_sm") {
         int per_sm = c->opt_blocks_per_sm;
-        if (per_sm <= 0) { Bind b(c); (c->opt_strict ? strict::render_occupancy : fast::render_occupancy)(c->opt_threads, &per_sm); }
+        if (per_sm <= 0) { Bind b(c); (c->opt_strict ? strict::render_occupancy : fast::render_occupancy)(c->opt_threads, false, &per_sm); }
         *value = per_sm;
     } else if (k == "frame_num") *value = c->frame_num;
     else return fail(c, "rtb_get_info", "unknown key");

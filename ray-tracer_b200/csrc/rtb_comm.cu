@@ -46,7 +46,8 @@ Nccl *nccl() {
         if (n.handle) break;
     }
     if (!n.handle) {
-        n.error = std::string("cannot load NCCL (libnccl.so.2): ") + (dlerror() ? dlerror() : "not found");
+        const char *why = dlerror();  // a second call would return NULL: the first one clears the message
+        n.error = std::string("cannot load NCCL (libnccl.so.2): ") + (why ? why : "not found");
         return &n;
     }
 #define RTB_NCCL_SYM(field, symbol)                                              \
@@ -110,10 +111,11 @@ int comm_barrier(rtb_ctx *c) {
 void close_peers(rtb_ctx *c) {
     if (c->peers_ipc)
         for (int r = 0; r < c->n_peers; r++)
-            if (r != c->comm_rank && c->peer_image[r]) cudaIpcCloseMemHandle(c->peer_image[r]);
+            if (r != c->peer_self && c->peer_image[r]) cudaIpcCloseMemHandle(c->peer_image[r]);
     for (int r = 0; r < RTB_MAX_PEERS; r++) c->peer_image[r] = nullptr;
     c->n_peers = 0;
     c->peers_ipc = false;
+    c->peer_self = -1;
 }
 
 }  // namespace
@@ -214,6 +216,7 @@ int rtb_peer_open(rtb_ctx *c, const unsigned char *handles, int world, int rank)
     close_peers(c);
     c->peers_ipc = true;
     c->n_peers = world;
+    c->peer_self = rank;
     for (int r = 0; r < world; r++) {
         if (r == rank) { c->peer_image[r] = c->d_image; continue; }
         cudaIpcMemHandle_t h;
@@ -222,7 +225,6 @@ int rtb_peer_open(rtb_ctx *c, const unsigned char *handles, int world, int rank)
         cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
         if (e != cudaSuccess) {
             c->n_peers = r;  // close what was opened
-            if (c->comm_rank != rank) c->comm_rank = rank;
             close_peers(c);
             return fail(c, "opening a peer's accumulation image", cudaGetErrorString(e));
         }

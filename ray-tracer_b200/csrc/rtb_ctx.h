@@ -33,6 +33,7 @@ struct rtb_ctx {
     std::vector<RtbImage> images;
     bool committed = false;
     bool mesh_uv_given = false;      // some mesh came with texture points (else the device flatten writes zeros instead of uploading them)
+    int opt_mega_early_pop = -1, tuned_mega_early_pop = 0;   // megakernel traversal variant (trav_run EARLY_POP): option (-1 = timed choice) / what the timed choice kept
     int opt_device_flatten = 2;      // meshes partitioned + flattened on the device: 0 never, 1 always, 2 = from 32768 triangles up
 
     // device scene
@@ -133,6 +134,7 @@ struct rtb_ctx {
     int *d_barrier = nullptr;
     float *peer_image[RTB_MAX_PEERS] = {};  // every rank's accumulation image mapped into this context (fused exchange)
     int n_peers = 0;
+    int peer_self = -1;              // index of this context's own image in peer_image (not an IPC mapping: never closed)
     bool peers_ipc = false;          // mappings came from CUDA IPC handles (one process per GPU): closed at destroy
     int peer_access[RTB_MAX_PEERS] = {};    // rtb_create_multi: this device can address device k directly
 };

@@ -118,9 +118,9 @@ struct LaunchConfig {
 
 #define RTB_DECLARE_VARIANT(ns)                                                                                     \
     namespace ns {                                                                                                  \
-    cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st);    \
+    cudaError_t launch_render(const RenderParams &p, bool brute, bool count, bool early_pop, LaunchConfig cfg, cudaStream_t st); \
     cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st);                                \
-    cudaError_t render_occupancy(int threads, int *blocks_per_sm);                                                  \
+    cudaError_t render_occupancy(int threads, bool early_pop, int *blocks_per_sm);                                  \
     cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);                     \
     cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st);         \
     cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm);                                \

@@ -282,7 +282,7 @@ __device__ __forceinline__ void path_begin_sample(const FrameConsts &f, V3 pdir,
 // (or nobody traverses any more); then the SHADE phase runs for all of them at once while the long
 // rays keep their traversal state, and everybody re-enters TRAVERSE together.
 // ---------------------------------------------------------------------------------------------
-template <bool BRUTE, bool COUNT>
+template <bool BRUTE, bool COUNT, bool EARLY_POP>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_megakernel(const RenderParams p) {
     const DScene &s = p.scene;
     const FrameConsts f = frame_consts(p.rd, p.cam);
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
         int quota = refill - __popc(__ballot_sync(FULL, mode == WAITING));
 #ifdef RTB_DYNAMIC_MASK
         if (mode == TRAVERSING) {
-            if (!BRUTE) trav_run(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
+            if (!BRUTE) trav_run<1, EARLY_POP>(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
             if (trav_done(T)) {
                 mode = WAITING;
                 pending = true;
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
 #else
         // all 32 lanes enter together: WAITING and IDLE lanes hold a finished traversal state
         // quota over the whole warp: the lanes that are not traversing now, plus max(1, refill - waiting) more
-        if (!BRUTE) trav_run(s, ray, T, FULL, (quota < 1 ? 1 : quota) + 32 - __popc(tmask), walk_min, cnt);
+        if (!BRUTE) trav_run<1, EARLY_POP>(s, ray, T, FULL, (quota < 1 ? 1 : quota) + 32 - __popc(tmask), walk_min, cnt);
         if (mode == TRAVERSING && trav_done(T)) {
             mode = WAITING;
             pending = true;
@@ -425,13 +425,17 @@ template <bool BRUTE> __global__ void primary_ids_kernel(const IdsParams p) {
     }
 }
 
-cudaError_t launch_render(const RenderParams &p, bool brute, bool count, LaunchConfig cfg, cudaStream_t st) {
+// early_pop: the variant of the traversal loop that fetches the stack entries with the node (trav_run, EARLY_POP)
+cudaError_t launch_render(const RenderParams &p, bool brute, bool count, bool early_pop, LaunchConfig cfg, cudaStream_t st) {
     if (brute) {
-        if (count) render_megakernel<true, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
-        else render_megakernel<true, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        if (count) render_megakernel<true, true, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        else render_megakernel<true, false, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+    } else if (early_pop) {
+        if (count) render_megakernel<false, true, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        else render_megakernel<false, false, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
     } else {
-        if (count) render_megakernel<false, true><<<cfg.blocks, cfg.threads, 0, st>>>(p);
-        else render_megakernel<false, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        if (count) render_megakernel<false, true, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
+        else render_megakernel<false, false, false><<<cfg.blocks, cfg.threads, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
@@ -443,8 +447,9 @@ cudaError_t launch_primary_ids(const IdsParams &p, bool brute, cudaStream_t st) 
     return cudaGetLastError();
 }
 
-cudaError_t render_occupancy(int threads, int *blocks_per_sm) {
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_megakernel<false, false>, threads, 0);
+cudaError_t render_occupancy(int threads, bool early_pop, int *blocks_per_sm) {
+    if (early_pop) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_megakernel<false, false, true>, threads, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_megakernel<false, false, false>, threads, 0);
 }
 
 #include "rtb_wavefront.cuh"

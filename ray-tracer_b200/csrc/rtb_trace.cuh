@@ -364,7 +364,7 @@ __device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &
 // NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
 // traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
 // max_rounds > 0: come back after that many rounds whatever the lanes did (a caller that polls a queue).
-template <int NODE_STEPS = 1>
+template <int NODE_STEPS = 1, bool EARLY_POP = false>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
                                          Counters &cnt, int max_rounds = 0) {
     (void)mask;
@@ -392,6 +392,16 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                     const float4 *N = s.nodes + 4 * cur;
                     float4 lo0, hi0, lo1, hi1;
                     load_node(N, lo0, hi0, lo1, hi1);
+                    // EARLY_POP: the two entries a pop (or two) of this step would bring up are fetched WITH the node, so
+                    // that their latency hides behind the node's and the cursor update below is register-only.  (Fetched
+                    // inside the pops, the loads sit on the critical path of the step: even predicated off, the second pop
+                    // waits for the first one's load -- 11 % of wf_traverse's stall samples.)  Measured
+                    // (profiles/r2_pop_ab.jsonl): the megakernel on the 1 M-triangle scene -5.5 % (nodes miss L1, the
+                    // step is long), every L1-resident scene and the wavefront traversal kernel +1 ... +4 % (two more
+                    // unconditional local loads on an L1 pipe that is 75 % busy): a variant of the megakernel only, taken
+                    // by the timed kernel choice where it wins.  stack[0] is the sentinel RTB_DONE and sp >= 1.
+                    int below1 = 0, below2 = 0;
+                    if (EARLY_POP) { below1 = T.stack[sp - 1]; below2 = T.stack[max(sp - 2, 0)]; }
                     // relative slack on the distance cull: a primitive's own t carries more rounding
                     // than the box planes do (cancellation in Moller-Trumbore), so keep boxes that
                     // start a hair beyond the current best
@@ -405,6 +415,7 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                     // four outcomes would otherwise run as four divergent paths
                     bool first0 = h0 && (!h1 || n0 <= n1);
                     int near = first0 ? r0 : r1, far = first0 ? r1 : r0;
+                    if (!EARLY_POP) {
                     // the stack cannot overflow: rtb_scene_commit refuses a tree higher than RTB_STACK - 2
                     RTB_ASSERT(!(h0 && h1) || sp < RTB_STACK);
                     if (h0 && h1) { T.stack[sp++] = top; top = far; }
@@ -415,6 +426,26 @@ __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T,
                     if (cur < 0 && leaf == 0) {  // first leaf: postpone it and keep walking
                         leaf = cur;
                         cur = top; sp = max(sp - 1, 0); top = T.stack[sp]; sp = max(sp, 1);
+                    }
+                    } else {
+                    const bool both = h0 && h1, any = h0 || h1;
+                    const bool take = any && near < 0 && leaf == 0;   // the first leaf: postpone it and keep walking
+                    if (take) leaf = near;
+                    const bool go_near = any && !take;   // the near child, not postponed
+                    const bool go_far = both && take;    // near was postponed: a push and a pop that cancel
+                    const bool push = both && !take;     // go near, keep far for later
+                    const bool pop1 = !go_near && !go_far;   // nothing to go to here: the register-held top
+                    // the stack cannot overflow: rtb_scene_commit refuses a tree higher than RTB_STACK - 2
+                    RTB_ASSERT(!push || sp < RTB_STACK);
+                    if (push) T.stack[sp] = top;
+                    int ncur = go_near ? near : (go_far ? far : top);
+                    int ntop = push ? far : (pop1 ? below1 : top);
+                    sp = push ? sp + 1 : (pop1 ? max(sp - 1, 1) : sp);
+                    const bool pop2 = pop1 && ncur < 0 && leaf == 0;   // the popped entry is a first leaf: postpone it, pop again
+                    if (pop2) leaf = ncur;
+                    cur = pop2 ? ntop : ncur;
+                    top = pop2 ? below2 : ntop;
+                    sp = pop2 ? max(sp - 1, 1) : sp;
                     }
                 }
             }

@@ -480,6 +480,31 @@ def test_edge_cases(tracer):
     assert b"Error from CUDA" in lib.rtb_last_error(tracer.ctx)
 
 
+def test_megakernel_early_pop_variant_is_bit_identical(tracer):
+    """the megakernel's second traversal-loop variant (stack entries fetched with the node: option mega_early_pop)
+    walks the same tree in the same order: same bits, same counters; the timed choice may pick either"""
+    for sid, p0, p1 in ((0, 0, 0), (3, 0, 0), (6, 3, 2)):
+        scene = _scene(sid, p0, p1)
+        tracer.setup(scene, 160, 120, 3, 6)
+        out = []
+        try:
+            tracer.set_option("kernel", 0)
+            tracer.set_option("counters", 1)
+            for variant in (0, 1):
+                tracer.set_option("mega_early_pop", variant)
+                img = np.zeros((120, 160, 3), np.float32)
+                f = tracer.render(img, 0, 31)
+                tracer.render(img, f, 32)
+                out.append((img, tracer.counters()))
+                assert int(tracer.info("mega_early_pop")) == variant
+        finally:
+            tracer.set_option("mega_early_pop", -1)
+            tracer.set_option("counters", 0)
+            tracer.set_option("kernel", 2)
+        assert (out[0][0] == out[1][0]).all()
+        assert out[0][1] == out[1][1]
+
+
 def test_pool_kernel_edge_cases(tracer):
     """The pooled persistent kernel and the streaming kernel on the shapes that stress their slot bookkeeping: fewer pixels than one warp's
     pool, an image smaller than a tile, zero bounces, an empty scene, a frame whose pixel count is not a multiple
