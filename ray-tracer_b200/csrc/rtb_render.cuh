@@ -282,6 +282,12 @@ __device__ __forceinline__ void path_begin_sample(const FrameConsts &f, V3 pdir,
 // (or nobody traverses any more); then the SHADE phase runs for all of them at once while the long
 // rays keep their traversal state, and everybody re-enters TRAVERSE together.
 // ---------------------------------------------------------------------------------------------
+// node steps between two ballots of the megakernel's NODE phase.  Measured with 7 resident blocks per SM (72 registers):
+// 2 steps -3.5 % on the 1 M-triangle tile share, -2 % on the Cornell scenes, +-0 on the cube scene; 3 steps +13 % on
+// the cube scene, 4 steps spill.  (With 6 blocks and 80 registers, round 1, two steps were 4 % slower.)
+#ifndef RTB_MEGA_NODE_STEPS
+#define RTB_MEGA_NODE_STEPS 2
+#endif
 template <bool BRUTE, bool COUNT, bool EARLY_POP>
 __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_megakernel(const RenderParams p) {
     const DScene &s = p.scene;
@@ -375,7 +381,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
         int quota = refill - __popc(__ballot_sync(FULL, mode == WAITING));
 #ifdef RTB_DYNAMIC_MASK
         if (mode == TRAVERSING) {
-            if (!BRUTE) trav_run<1, EARLY_POP>(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
+            if (!BRUTE) trav_run<RTB_MEGA_NODE_STEPS, EARLY_POP>(s, ray, T, tmask, quota < 1 ? 1 : quota, walk_min, cnt);
             if (trav_done(T)) {
                 mode = WAITING;
                 pending = true;
@@ -384,7 +390,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_MIN_BLOCKS) render_mega
 #else
         // all 32 lanes enter together: WAITING and IDLE lanes hold a finished traversal state
         // quota over the whole warp: the lanes that are not traversing now, plus max(1, refill - waiting) more
-        if (!BRUTE) trav_run<1, EARLY_POP>(s, ray, T, FULL, (quota < 1 ? 1 : quota) + 32 - __popc(tmask), walk_min, cnt);
+        if (!BRUTE) trav_run<RTB_MEGA_NODE_STEPS, EARLY_POP>(s, ray, T, FULL, (quota < 1 ? 1 : quota) + 32 - __popc(tmask), walk_min, cnt);
         if (mode == TRAVERSING && trav_done(T)) {
             mode = WAITING;
             pending = true;

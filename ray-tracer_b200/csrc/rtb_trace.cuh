@@ -362,7 +362,7 @@ __device__ __forceinline__ void load_node(const float4 *N, float4 &lo0, float4 &
 #endif
 // quota: leave once this many lanes of the WARP hold a finished (or no) ray; <= 0 = run to completion.
 // NODE_STEPS: node steps between two ballots of the NODE phase (measured: 2 is +1-2 % in the wavefront
-// traversal kernel, -4 % in the megakernel, whose warps also carry the shading state).
+// traversal kernel and, since the megakernel runs 7 blocks per SM, +2-3.5 % there as well: rtb_render.cuh).
 // max_rounds > 0: come back after that many rounds whatever the lanes did (a caller that polls a queue).
 template <int NODE_STEPS = 1, bool EARLY_POP = false>
 __device__ __forceinline__ void trav_run(const DScene &s, const Ray &r, Trav &T, unsigned mask, int quota, int walk_min,
