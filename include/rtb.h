@@ -276,12 +276,14 @@ int rtb_counters(rtb_ctx *ctx, RtbCounters *out);
  * (default; bit-identical images; beyond the packing limits of kernels 1, 3, 4 -- reflection_limit > 255 or
  * rays_per_pixel >= 2^24 -- the choice is the megakernel, while pinning 1, 3 or 4 refuses such a frame);
  * "tune_set" (kernels the timed choice tries: 1 megakernel | 2 wavefront | 8 pooled | 16 streaming; default 3);
+ * "mega_early_pop" -1 / 0 / 1 (the megakernel's traversal loop fetches the stack entries with the node: -1 = the timed
+ * choice keeps the faster variant -- default; same image either way);
  * "strict_fp" 0/1 (kernels built with -fmad=false); "builder" 0 = Karras LBVH, 1 = PLOC (next commit; 2 = host
  * full-sweep SAH, a tree-quality yardstick for experiments only); "ploc_radius"; "device_flatten" 0 = meshes are
  * partitioned + flattened on the host, 1 = on the device, 2 = on the device from 32768 triangles up (default; next
  * commit; same arrays either way);
  * "large_split", "max_large", "reference_bvh_quirks" (next commit); "walk_min", "refill", "wf_refill",
- * "wf_rebuild", "wf_groups", "wf_streams" (traversal / wavefront policy, 0 = tuned); "block_threads";
+ * "wf_rebuild", "wf_groups", "wf_streams" (traversal / wavefront policy, 0 = tuned; up to 8 row groups in flight); "block_threads";
  * "blocks_per_sm"; "wf_timing" (events around every wavefront launch of the next frame);
  * "run_ahead" (frames the host may enqueue ahead of the device, 0 = unbounded) and "wf_pace" (wavefront
  * iterations the host may run ahead, 0 = unbounded): host pacing knobs, measured without effect, off by default;

@@ -23,6 +23,9 @@
 //   A {thr.xyz, cur_n}   B {col.xyz, rng bits}   C {acc.xyz, sample << 8 | bounce}
 //   O {origin.xyz, first node below the root}   D {direction.xyz, second node}   H {t, u, v, code}
 
+#ifndef RTB_WF_NODE_STEPS
+#define RTB_WF_NODE_STEPS 2   // node steps between two ballots in wf_traverse (measured: 1 is 1-2 % slower, 3 see DESIGN.md)
+#endif
 #ifndef RTB_SHADE_MIN_BLOCKS
 #define RTB_SHADE_MIN_BLOCKS 4
 #endif
@@ -224,7 +227,7 @@ __global__ void __launch_bounds__(RTB_BLOCK_THREADS, RTB_TRAV_MIN_BLOCKS) wf_tra
         // all 32 lanes enter together (lanes without a ray hold a finished state): while the queue has
         // rays, leave the tree when `refill` lanes are free; afterwards run to the end
         // (the quota counts finished lanes of the whole warp: the lanes that are free now, plus at least one)
-        if (!BRUTE) trav_run<2>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
+        if (!BRUTE) trav_run<RTB_WF_NODE_STEPS>(s, ray, T, FULL, exhausted ? 0 : max(p.refill, 33 - __popc(busy_mask)), p.walk_min, cnt);
 #endif
     }
     if (COUNT && p.counters) {
