@@ -934,7 +934,7 @@ int launch_frame_wavefront(rtb_ctx *c, int time_ms, int frame_num) {
             unsigned int *cnt = c->d_wf_counts + 8 * l;
             g.count[0] = cnt; g.count[1] = cnt + 1; g.p.fetch = cnt + 2; g.tcount[0] = cnt + 4; g.tcount[1] = cnt + 5;
             g.block_count = c->d_wf_block_count + l * (((slots + 255) / 256) + 2);
-            g.shade_blocks = (int)std::min<size_t>((g.slot_count + 255) / 256, (size_t)c->num_sms * c->wf_shade_per_sm);
+            g.shade_blocks = (int)std::min<size_t>((g.slot_count + RTB_SHADE_THREADS - 1) / RTB_SHADE_THREADS, (size_t)c->num_sms * c->wf_shade_per_sm);
             e = cudaMemsetAsync(cnt, 0, 8 * sizeof(unsigned int), g.st);
             if (e == cudaSuccess) e = launch_shade(g, 1, 1, 0);
             active++;

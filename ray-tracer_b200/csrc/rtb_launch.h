@@ -32,6 +32,9 @@ struct IdsParams {
 };
 
 // ---- wavefront variant (rtb_wavefront.cuh) -----------------------------------------------------
+#ifndef RTB_SHADE_THREADS
+#define RTB_SHADE_THREADS 256   // block size of wf_shade (grid-stride over the live queue)
+#endif
 struct WfState {
     float4 *A, *B, *C, *O, *D, *H;
 };

@@ -40,7 +40,7 @@ __device__ __forceinline__ void wf_slot_to_pixel(const WfParams &p, int slot, in
 }
 
 template <bool BRUTE, bool COUNT>
-__global__ void __launch_bounds__(256, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfParams p) {
+__global__ void __launch_bounds__(RTB_SHADE_THREADS, RTB_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfParams p) {
     const DScene &s = p.scene;
     const FrameConsts f = frame_consts(p.rd, p.cam);
     const unsigned int n = p.first ? (unsigned int)p.slot_count : *p.n_in;
@@ -305,11 +305,11 @@ cudaError_t launch_wf_rebuild(int slot_base, int n_slots, const unsigned char *a
 
 cudaError_t launch_wf_shade(const WfParams &p, bool brute, bool count, int blocks, cudaStream_t st) {
     if (brute) {
-        if (count) wf_shade_kernel<true, true><<<blocks, 256, 0, st>>>(p);
-        else wf_shade_kernel<true, false><<<blocks, 256, 0, st>>>(p);
+        if (count) wf_shade_kernel<true, true><<<blocks, RTB_SHADE_THREADS, 0, st>>>(p);
+        else wf_shade_kernel<true, false><<<blocks, RTB_SHADE_THREADS, 0, st>>>(p);
     } else {
-        if (count) wf_shade_kernel<false, true><<<blocks, 256, 0, st>>>(p);
-        else wf_shade_kernel<false, false><<<blocks, 256, 0, st>>>(p);
+        if (count) wf_shade_kernel<false, true><<<blocks, RTB_SHADE_THREADS, 0, st>>>(p);
+        else wf_shade_kernel<false, false><<<blocks, RTB_SHADE_THREADS, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
@@ -326,7 +326,7 @@ cudaError_t launch_wf_traverse(const WfParams &p, bool brute, bool count, int bl
 }
 
 cudaError_t wf_occupancy(int *shade_blocks_per_sm, int *traverse_blocks_per_sm) {
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false, false>, 256, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade_kernel<false, false>, RTB_SHADE_THREADS, 0);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(traverse_blocks_per_sm, wf_traverse_kernel<false, false>, RTB_BLOCK_THREADS, 0);
 }
