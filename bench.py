@@ -15,13 +15,14 @@ e2e    = the same metric through the reference-facing entry point rtb_render() =
          VariableRenderData*, int): host image in, host image out, H2D and D2H inside the timed region.
 N > 1  : one process per GPU (torchrun).  Two partitionings, --sharding:
          tiles   row-cyclic bands of the SAME frame (strong scaling, image bit-identical to 1 GPU),
-                 NCCL all-gather of the bands inside the timed region;
+                 the exchange of the bands inside the timed region;
          slices  sample slices of a progressive render: every rank renders the whole frame for its
                  own frames (current_time_ms = base + rank), NCCL all-reduce of the accumulation
                  buffer inside the timed region; a step yields N x spp samples (weak scaling).
-         auto    (default) tiles for the 4K configs (C4: BASELINE.json's tile-sharded config), slices
-                 otherwise: a 1080p frame cut in 8 leaves 0.26 M pixels per GPU, too few rays per
-                 launch to fill 148 SMs (measured at N = 2 on C3: tiles 83 % efficient).
+         auto    (default) tiles for C4 (BASELINE.json's tile-sharded config), slices otherwise (C5 is
+                 the survey's sample-slice config; a 1080p frame cut in 8 leaves 0.26 M pixels per GPU,
+                 too few rays per launch to fill 148 SMs: measured at N = 2 on C3, tiles 83 % efficient).
+         Both exchanges run INSIDE the library (rtb_comm.cu); tiles default to the fused peer-store exchange.
 --impl reference : the reference's OWN CUDA build (baseline/_ref, unmodified sources, resolution
          constants patched) on the same workload at a bounded spp per step (a rate, spp independent);
          if that library is absent, the reference source on the host cores (oracle/_ref), else the C port.
@@ -302,7 +303,10 @@ class Job:
         sid, p0, p1, W, H, spp, bounces = WORKLOADS[workload]
         self.W, self.H, self.spp, self.bounces = W, H, spp, bounces
         if sharding == "auto":
-            sharding = "tiles" if W * H >= 3840 * 2160 else "slices"
+            # C4 is the tile-sharded config (partitioning A), C5 the sample-slice one (B: GPU g renders
+            # the frames f with f mod N == g, its own time seeds, one all-reduce); the 1080p-and-below configs leave too
+            # few pixels per GPU for tiles
+            sharding = "tiles" if workload == "C4" else "slices"
         if world == 1:
             sharding = "none"
         self.sharding = sharding
