@@ -107,6 +107,48 @@ def test_converged_radiance_vs_reference_cuda(kernel):
 
 
 @needs_ref
+def test_c5_sample_slices_vs_the_reference_progressive_render():
+    """C5 as SURVEY.md 8(d) specifies it (at 320x256, the size the reference library here is built for): a progressive
+    render of 128 frames x 128 spp = 16 384 spp; GPU g of 8 renders the frames f with f mod 8 == g, current_time_ms =
+    1000 + f; the per-GPU running means are summed and divided by 8 (the all-reduce of partitioning B, emulated rank
+    by rank on one device: the arithmetic of rtb_comm.cu's slice exchange).  The checker is the reference's OWN CUDA
+    build rendering the same 128 frames one after the other through its running mean (src/raytracer.cu:107-112).
+    Bars: RMSE < 1e-3 and PSNR > 45 dB (the north_star's), with the noise of the estimate itself far below (16 384
+    spp); a wrong seed, weight or frame count shows as ~1e-2."""
+    frames, spp, bounces, world = 128, 128, 8, 8
+    ref = ob.RefCuda(W, H)
+    ref.init(0, 0, 0, spp, bounces, True)
+    r_img = np.zeros((H, W, 3), np.float32)
+    for f in range(frames):
+        ref.render_kernel(r_img, f, 1000 + f)
+    scene = rtb.Scene(0)
+    tr = rtb.Tracer(0).setup(scene, W, H, spp, bounces)
+    acc = np.zeros((H, W, 3), np.float64)
+    for rank in range(world):
+        tr.reset()
+        tr.render_device(frames // world, 1000 + rank, world)   # frames rank, rank + 8, ...
+        tr.sync()
+        part, n = tr.download()
+        assert n == frames // world
+        acc += part
+    sliced = (acc / world).astype(np.float32)
+    # and the same frames on ONE context, in order: what the slices must reproduce up to the order of the float sums
+    tr.reset()
+    tr.render_device(frames, 1000, 1)
+    tr.sync()
+    whole, n = tr.download()
+    tr.close()
+    assert n == frames
+    rmse = float(np.sqrt(((sliced - r_img) ** 2).mean()))
+    psnr = 20 * np.log10(max(1.0, float(r_img.max())) / max(rmse, 1e-12))
+    own = float(np.abs(sliced - whole).max())
+    print(f"C5 at {W}x{H}: sliced vs reference progressive render RMSE {rmse:.3e}, PSNR {psnr:.1f} dB; sliced vs own 1-GPU render max abs diff {own:.3e}")
+    _record("c5_slices_320x256_vs_reference_cuda", frames=frames, spp_per_frame=spp, ranks=world, rmse=rmse, psnr_db=float(psnr), max_abs_diff_vs_own_progressive=own)
+    assert rmse < 1e-3 and psnr > 45
+    assert own < 5e-5 * max(1.0, float(whole.max()))
+
+
+@needs_ref
 def test_reference_render_entry_point_matches_its_kernel():
     """render() (src/dispatch.cu:156) and the harness launch of the same kernel agree bit for bit."""
     ref = ob.RefCuda(W, H)
