@@ -85,15 +85,16 @@ def test_ids_and_radiance_vs_reference_cuda(sid, p0, p1):
 @pytest.mark.parametrize("kernel", [0, 1])
 def test_converged_radiance_vs_reference_cuda(kernel):
     """north_star acceptance: converged radiance within RMSE < 1e-3 (PSNR > 45 dB) of the reference
-    render at matched spp -- default build of both sides, glass scene and monkey scene, 128 spp,
-    megakernel and wavefront."""
-    for sid in (3, 0, 7):   # 7: OBJ + MTL scene (image-textured, glass, emissive and glossy meshes)
+    render at matched spp -- default build of both sides, 128 spp, megakernel and wavefront."""
+    # wavefront pair: all eight scenes; megakernel: glass, monkey room and the OBJ + MTL scene (image-textured, glass,
+    # emissive and glossy meshes)
+    for sid, p0, p1 in (SCENES if kernel == 1 else [(3, 0, 0), (0, 0, 0), (7, 0, 0)]):
         spp, bounces = 128, 5
         ref = ob.RefCuda(W, H)
-        ref.init(sid, 0, 0, spp, bounces, True)
+        ref.init(sid, p0, p1, spp, bounces, True)
         r_img = np.zeros((H, W, 3), np.float32)
         ref.render_kernel(r_img, 0, 2024)
-        scene = rtb.Scene(sid, 0, 0)
+        scene = rtb.Scene(sid, p0, p1)
         tr = rtb.Tracer(0)
         tr.set_option("kernel", kernel)
         tr.setup(scene, W, H, spp, bounces)
@@ -101,6 +102,7 @@ def test_converged_radiance_vs_reference_cuda(kernel):
         tr.render(img, 0, 2024)
         tr.close()
         rmse = float(np.sqrt(((img - r_img) ** 2).mean()))
+        _record(f"converged_128spp_scene{sid}_kernel{kernel}", rmse=rmse, bit_identical_floats=float((img == r_img).mean()))
         psnr = 20 * np.log10(max(1.0, float(r_img.max())) / max(rmse, 1e-12))
         print(f"scene {sid} kernel {kernel} at {spp} spp: RMSE {rmse:.3e}, PSNR {psnr:.1f} dB, bit-identical {float((img == r_img).mean()):.4f}")
         assert rmse < 1e-3 and psnr > 45
