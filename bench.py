@@ -284,7 +284,20 @@ def reference_arm(args):
         line = dict(base, value=cb["value"], ms_per_step=None, cpu_baseline=cb, gpu_launches=0,
                     e2e={"value": cb["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     config=config, reference_build="reference CUDA library absent; host build of the reference source")
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the run's one JSON line, on the process's real stdout (see main)"""
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 KERNEL_DESC = {0: "persistent megakernel", 1: "wavefront: wf_shade + persistent wf_traverse per path segment",
@@ -501,6 +514,12 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    # The contract is ONE JSON line on stdout.  Libraries print on fd 1 as well (NCCL's version banner at the first
+    # communicator, for one): from here on fd 1 is stderr, and the line goes to the real stdout through emit().
+    sys.stdout.flush()
+    global _REAL_STDOUT
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return reference_arm(args)
 
@@ -610,7 +629,7 @@ def main():
             line["c4_tiles"] = c4
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg(args.workload, 1)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
