@@ -259,8 +259,9 @@ def reference_arm(args):
         clocks = sampler.stop()
         ms_step = sum(kernel_ms) / len(kernel_ms)
         # end to end through the reference's own render() (src/dispatch.cu:156), host image in and out: wall clock,
-        # same spp per step; as many of the K steps as fit in ~2.5 minutes
-        e2e_steps = max(1, min(args.steps, int(150.0 / max(ms_step / 1e3, 1e-3))))
+        # same spp per step; as many of the K steps as fit in about a minute (a C3 step of the reference is 6.3 s: with
+        # the driver's K = 20 the kernel-timed part alone is 2.4 minutes)
+        e2e_steps = max(1, min(args.steps, int(60.0 / max(ms_step / 1e3, 1e-3))))
         img2 = np.zeros((H, W, 3), np.float32)
         ref.render(img2, 0, 899)
         wall = []
